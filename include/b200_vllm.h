@@ -1,0 +1,281 @@
+/*
+ * b200_vllm.h — C ABI of libb200vllm.so, the sm_100a implementation of vLLM's
+ * decode-step hot path.  Every entry point takes plain device pointers, sizes,
+ * strides (in ELEMENTS unless a name ends in _bytes) and a CUDA stream; no
+ * torch types cross this boundary.  All outputs are caller-allocated, nothing
+ * is allocated or synchronised inside (CUDA-graph capturable), and every
+ * function returns 0 on success or a negative B200_ERR_* code *before* any
+ * launch when a precondition fails (the Python shim turns it into
+ * RuntimeError, like STD_TORCH_CHECK does in the reference).
+ *
+ * Each function cites the reference interface it replaces, as path:line under
+ * /root/reference (vllm-project/vllm).
+ */
+#ifndef B200_VLLM_H_
+#define B200_VLLM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b200_stream_t; /* cudaStream_t */
+
+/* ---- error codes ------------------------------------------------------- */
+#define B200_OK 0
+#define B200_ERR_INVALID_ARG (-1)   /* shape / dtype / enum precondition     */
+#define B200_ERR_ALIGNMENT (-2)     /* pointer or stride alignment           */
+#define B200_ERR_UNSUPPORTED (-3)   /* valid in the reference, not built here */
+#define B200_ERR_CUDA (-4)          /* a CUDA runtime / driver call failed   */
+#define B200_ERR_WORKSPACE (-5)     /* workspace too small                   */
+
+/* ---- dtype enums ------------------------------------------------------- */
+/* activation / query / output scalar types */
+#define B200_DT_F32 0
+#define B200_DT_F16 1
+#define B200_DT_BF16 2
+/* kv_cache_dtype: "auto" (= same as activations), "fp8"/"fp8_e4m3", "fp8_e5m2"
+ * (csrc/attention/dtype_fp8.cuh:21, quant_utils.cuh:575-613) */
+#define B200_KV_AUTO 0
+#define B200_KV_FP8_E4M3 1
+#define B200_KV_FP8_E5M2 2
+
+/* Library / build identification. */
+const char* b200_version(void);          /* "b200vllm <n> sm_100a"            */
+const char* b200_last_error(void);       /* thread-local detail for last <0  */
+int b200_num_kernels_launched(void);     /* running launch counter (bench)   */
+
+/* ------------------------------------------------------------------------
+ * KV-cache write.
+ * Replaces: reshape_and_cache_flash
+ *   host   csrc/libtorch_stable/cache_kernels.cu:801-871
+ *   kernel csrc/libtorch_stable/cache_kernels.cu:320-406
+ *   schema csrc/libtorch_stable/torch_bindings.cpp:915-921
+ *   python vllm/_custom_ops.py:2631-2650
+ * For every t < num_tokens with slot = slot_mapping[t] >= 0:
+ *   key_cache  [slot / block_size][slot % block_size][h][:] = cvt(key  [t][h][:])
+ *   value_cache[slot / block_size][slot % block_size][h][:] = cvt(value[t][h][:])
+ * cvt = identity (B200_KV_AUTO) or fp8(float(x) / scale) RN-even, satfinite
+ * (quant_utils.cuh:480-503).  The cache is addressed with explicit strides so
+ * NHD, HND and the K|V-interleaved page layouts all work:
+ *   addr = cache + block*block_stride + offset*page_stride + h*head_stride.
+ * k_scale/v_scale: device fp32, 1 element (kv_scale_stride==0) or one per
+ * head (kv_scale_stride==1); ignored for B200_KV_AUTO.
+ * ---------------------------------------------------------------------- */
+int b200_reshape_and_cache_flash(
+    const void* key, const void* value, void* key_cache, void* value_cache,
+    const int64_t* slot_mapping, int64_t num_tokens, int num_heads,
+    int head_size, int block_size, int64_t key_stride, int64_t value_stride,
+    int64_t block_stride, int64_t page_stride, int64_t head_stride,
+    int src_dtype, int kv_dtype, const float* k_scale, const float* v_scale,
+    int kv_scale_stride, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Slot mapping (producer of the cache-write indices; integer, bit-exact).
+ * Replaces: BlockTable.compute_slot_mapping + its Triton kernel
+ *   vllm/v1/worker/block_table.py:201-229,412-475
+ * slot[t] = block_table[req(t)][pos[t] / block_size] * block_size
+ *           + pos[t] % block_size          for t in [query_start_loc[r],
+ *                                          query_start_loc[r+1]), r < num_reqs
+ * slot[t] = -1 (PAD_SLOT_ID)               for num_tokens <= t < num_slots
+ *                                          (CUDA-graph padding tail).
+ * ---------------------------------------------------------------------- */
+int b200_compute_slot_mapping(
+    int64_t* slot_mapping, int64_t num_slots, int64_t num_tokens,
+    const int32_t* query_start_loc, int num_reqs, const int64_t* positions,
+    const int32_t* block_table,
+    int64_t block_table_stride, int block_size, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Paged-attention decode (one query token per sequence), split-KV + combine,
+ * GQA-grouped: one CTA serves all q-heads of one kv-head so K/V pages are
+ * read once.
+ * Replaces (same math, same cache layout):
+ *   legacy   paged_attention_v1/v2     vllm/_custom_ops.py:120-163 (ROCm port
+ *            csrc/rocm/attention.cu:320-1520; design docs/design/paged_attention.md)
+ *   current  kernel_unified_attention 3D + reduce_segments
+ *            vllm/v1/attention/ops/triton_unified_attention.py:179-681,685-771
+ *   caller   FlashAttentionImpl.forward vllm/v1/attention/backends/flash_attn.py:1085-1110
+ *
+ * out[s][h][:] = softmax(scale * q[s][h] . K[s][0:len_s]^T) V[s][0:len_s]
+ * with K/V rows of sequence s found through block_table[s][0:ceil(len/bs)].
+ * fp8 caches: K = k_scale * fp8, V = v_scale * fp8 (per-tensor device scalars).
+ * Sequences with seq_lens[s] == 0 produce zeros.
+ *
+ * workspace: fp32 scratch for the split partials; size from
+ * b200_paged_decode_workspace_bytes().  num_splits == 0 lets the library pick
+ * (deterministic in (num_seqs, num_kv_heads, max_seq_len) only -> graph safe).
+ * out_lse (optional, fp32 [num_seqs][num_q_heads]): natural-log LSE per head
+ * (needed by decode-context-parallel callers, backend.py:791-816).
+ * ---------------------------------------------------------------------- */
+typedef struct b200_paged_decode_params {
+  void* out;                 /* [num_seqs][num_q_heads][head_size], q dtype  */
+  const void* query;         /* [num_seqs][num_q_heads][head_size]           */
+  const void* key_cache;     /* paged, see strides                           */
+  const void* value_cache;
+  const int32_t* block_table; /* [num_seqs][block_table_stride]              */
+  const int32_t* seq_lens;    /* [num_seqs]                                  */
+  const float* k_scale;       /* device scalar or NULL (=1)                  */
+  const float* v_scale;
+  float* out_lse;             /* optional                                    */
+  void* workspace;
+  size_t workspace_bytes;
+  int64_t q_stride_seq, q_stride_head;     /* elements                      */
+  int64_t out_stride_seq, out_stride_head; /* elements                      */
+  int64_t kv_block_stride, kv_page_stride, kv_head_stride; /* elements, K  */
+  int64_t v_block_stride, v_page_stride, v_head_stride;    /* elements, V  */
+  int64_t block_table_stride;
+  int64_t num_blocks;         /* extent of the cache (TMA bound)             */
+  int num_seqs, num_q_heads, num_kv_heads, head_size, block_size;
+  int max_seq_len;            /* upper bound on seq_lens (host knowledge)    */
+  int q_dtype;                /* B200_DT_F16 / B200_DT_BF16                  */
+  int kv_dtype;               /* B200_KV_*                                   */
+  int num_splits;             /* 0 = auto                                    */
+  float scale;                /* softmax scale                               */
+  float logits_soft_cap;      /* 0 = off                                     */
+  int sliding_window;         /* 0 = off; else attend to last W tokens       */
+} b200_paged_decode_params;
+
+size_t b200_paged_decode_workspace_bytes(int num_seqs, int num_q_heads,
+                                         int head_size, int num_splits);
+int b200_paged_decode_pick_splits(int num_seqs, int num_kv_heads,
+                                  int max_seq_len, int sm_count);
+int b200_paged_attention_decode(const b200_paged_decode_params* p,
+                                b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Two-way (out, lse) merge.
+ * Replaces: merge_attn_states
+ *   csrc/libtorch_stable/attention/merge_attn_states.cu:19-257,259-362
+ *   schema csrc/libtorch_stable/torch_bindings.cpp:354-362
+ * output[t][h][:] = (e^{lp-m} P + e^{ls-m} S) / (e^{lp-m} + e^{ls-m}),
+ * output_lse = m + log(sum); +-inf LSEs are treated as -inf.
+ * prefix/suffix outputs are [tokens][heads][head_size] (stride given in
+ * elements per token / per head), LSEs are fp32 [heads][tokens].
+ * ---------------------------------------------------------------------- */
+int b200_merge_attn_states(void* output, float* output_lse,
+                           const void* prefix_output, const float* prefix_lse,
+                           const void* suffix_output, const float* suffix_lse,
+                           int64_t num_tokens, int num_heads, int head_size,
+                           int64_t out_stride_tok, int64_t out_stride_head,
+                           int64_t p_stride_tok, int64_t p_stride_head,
+                           int64_t s_stride_tok, int64_t s_stride_head,
+                           int64_t lse_stride_head, int dtype,
+                           b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * FP8 (e4m3) activation quantisation.
+ * Replaces: csrc/libtorch_stable/quantization/w8a8/fp8/common.cu
+ *   static_scaled_fp8_quant            :183-306  (kernel :13-76)
+ *   dynamic_scaled_fp8_quant           :308-354  (kernels :78-135)
+ *   dynamic_per_token_scaled_fp8_quant :356-420  (kernel :137-179)
+ *   conversion csrc/quantization/w8a8/fp8/common.cuh:57-76
+ *   schemas csrc/libtorch_stable/torch_bindings.cpp:645-659
+ * input [num_tokens][hidden] (row stride in elements), out e4m3 bytes.
+ * ---------------------------------------------------------------------- */
+/* out = e4m3(clamp(x * (1/scale[g]), +-448)); scale indexed
+ * scale[(m / group_m) * scale_stride_i + (n / group_n) * scale_stride_j]. */
+int b200_static_scaled_fp8_quant(void* out, const void* input,
+                                 const float* scale, int64_t num_tokens,
+                                 int hidden, int64_t in_row_stride,
+                                 int64_t out_row_stride, int group_m,
+                                 int group_n, int64_t scale_stride_i,
+                                 int64_t scale_stride_j, int dtype,
+                                 b200_stream_t stream);
+/* scale[0] = max|x| / 448 over the whole tensor; out = e4m3(clamp(x*(1/scale))) */
+int b200_dynamic_scaled_fp8_quant(void* out, const void* input, float* scale,
+                                  int64_t num_tokens, int hidden,
+                                  int64_t in_row_stride, int64_t out_row_stride,
+                                  int dtype, b200_stream_t stream);
+/* scale[m] = max(min(amax_m, ub) / 448, 1/(448*512)); out = e4m3(clamp(x/scale[m])) */
+int b200_dynamic_per_token_scaled_fp8_quant(
+    void* out, const void* input, float* scales, const float* scale_ub,
+    int64_t num_tokens, int hidden, int64_t in_row_stride,
+    int64_t out_row_stride, int dtype, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * NVFP4 activation quantisation (e2m1 codes + e4m3 scale per 16 elements).
+ * Replaces: scaled_fp4_quant(.out)
+ *   csrc/libtorch_stable/quantization/fp4/nvfp4_quant_kernels.cu:39-113,188-281
+ *   math   csrc/libtorch_stable/quantization/fp4/nvfp4_utils.cuh:221-302
+ *   SF offset nvfp4_utils.cuh:168-199
+ *   schema csrc/libtorch_stable/torch_bindings.cpp:218-222
+ * input [m][n] fp16/bf16 contiguous; output [m][out_n/2] bytes (two codes per
+ * byte, even element in the low nibble), out_n >= n (columns past n encode 0).
+ * swizzled != 0: output_sf is the [ceil(m/128)][ceil(out_n/64)][32][4][4]
+ * tensor-core layout and every padded SF is written (0); else row-major
+ * [m][out_n/16].
+ * ---------------------------------------------------------------------- */
+int b200_scaled_fp4_quant(void* output, void* output_sf, const void* input,
+                          const float* input_global_scale, int m, int n,
+                          int out_n, int swizzled, int dtype,
+                          b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * FP8 W8A8 GEMM (tcgen05 / TMEM / TMA).
+ * Replaces: cutlass_scaled_mm
+ *   host checks csrc/libtorch_stable/quantization/w8a8/cutlass/scaled_mm_entry.cu:197-270
+ *   sm100 configs .../c3x/scaled_mm_sm100_fp8_dispatch.cuh:100-194,243-296
+ *   epilogue csrc/libtorch_stable/cutlass_extensions/epilogue/scaled_mm_epilogues_c3x.hpp:150-183
+ *   schema csrc/libtorch_stable/torch_bindings.cpp:116-119
+ * out[M][N] = cast( a_scales[m|0] * b_scales[n|0] * sum_k A[m][k] B[k][n] ) + bias[n]
+ * A [M][K] e4m3 row-major (lda elements), B "column-major [K][N]" i.e. stored
+ * [N][K] K-contiguous (ldb elements), out row-major (ldc), fp32 accumulate.
+ * a_scales has 1 or M entries, b_scales 1 or N.  K % 16 == 0, N % 16 == 0.
+ * ---------------------------------------------------------------------- */
+int b200_scaled_mm_fp8(void* out, const void* a, const void* b,
+                       const float* a_scales, const float* b_scales,
+                       const void* bias, int M, int N, int K, int64_t lda,
+                       int64_t ldb, int64_t ldc, int a_scales_numel,
+                       int b_scales_numel, int out_dtype, void* workspace,
+                       size_t workspace_bytes, b200_stream_t stream);
+/* Optional split-K scratch for the decode regime (M <= 128): fp32 [M][N] plus
+ * tile counters.  Zero it ONCE after allocation; the kernels leave it zeroed.
+ * workspace == NULL disables split-K. */
+size_t b200_scaled_mm_workspace_bytes(int M, int N);
+
+/* ------------------------------------------------------------------------
+ * NVFP4 block-scaled GEMM (tcgen05.mma kind::mxf4nvf4, scale_vec::4X).
+ * Replaces: cutlass_scaled_fp4_mm
+ *   entry  csrc/libtorch_stable/quantization/fp4/nvfp4_scaled_mm_entry.cu:41-69
+ *   kernel csrc/libtorch_stable/quantization/fp4/nvfp4_scaled_mm_kernels.cu:46-137,190-248
+ *   checks nvfp4_scaled_mm_kernels.cu:279-347
+ *   schema csrc/libtorch_stable/torch_bindings.cpp:187-190
+ * out[M][N] = cast( alpha * sum_k (A4[m][k] SFA[m][k/16]) (B4[n][k] SFB[n][k/16]) )
+ * A [M][K/2] bytes, B [N][K/2] bytes (K-contiguous, two e2m1 per byte),
+ * SFA / SFB e4m3 in the swizzled 128x4 layout with padded shapes
+ * [ru(M,128)][ru(K/16,4)] / [ru(N,128)][ru(K/16,4)].  K % 32 == 0, N % 32 == 0.
+ * alpha: device fp32 scalar.
+ * ---------------------------------------------------------------------- */
+int b200_scaled_mm_nvfp4(void* out, const void* a, const void* b,
+                         const void* sfa, const void* sfb, const float* alpha,
+                         int M, int N, int K, int64_t ldc, int out_dtype,
+                         b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Element-wise companions of the quantised linears on the decode step
+ * (SURVEY 8f-1).  Not on the first-bar path; provided so a whole decode layer
+ * can run on this library.
+ *   rms_norm / fused_add_rms_norm  csrc/libtorch_stable/layernorm_kernels.cu
+ *   silu_and_mul                   csrc/libtorch_stable/activation_kernels.cu
+ *   rotary_embedding (neox)        csrc/libtorch_stable/pos_encoding_kernels.cu
+ * ---------------------------------------------------------------------- */
+int b200_rms_norm(void* out, const void* input, const void* weight,
+                  void* residual /* nullable: fused add, updated in place */,
+                  int64_t num_tokens, int hidden, int64_t in_row_stride,
+                  float eps, int dtype, b200_stream_t stream);
+int b200_silu_and_mul(void* out, const void* input, int64_t num_tokens, int d,
+                      int dtype, b200_stream_t stream);
+int b200_rotary_embedding_neox(void* query, void* key, const int64_t* positions,
+                               const void* cos_sin_cache, int64_t num_tokens,
+                               int num_q_heads, int num_kv_heads, int head_size,
+                               int rot_dim, int64_t q_stride_tok,
+                               int64_t k_stride_tok, int dtype,
+                               b200_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_VLLM_H_ */

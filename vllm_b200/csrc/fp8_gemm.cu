@@ -1,0 +1,411 @@
+// FP8 W8A8 GEMM on tcgen05 / TMEM / TMA:  out = a_s * b_s * (A @ B^T) (+ bias).
+// Reference semantics: cutlass_scaled_mm, csrc/libtorch_stable/quantization/w8a8/cutlass/
+// scaled_mm_entry.cu:197-270 (checks), c3x/scaled_mm_sm100_fp8_dispatch.cuh:100-296
+// (tile / swap-AB dispatch by M), epilogue scaled_mm_epilogues_c3x.hpp:150-183.
+//
+// B200 design.  Both operands are K-major (A [M][K]; B stored [N][K]), so either can
+// sit on the 128-row UMMA "M" side.  The CTA computes a 128 x BN fp32 tile in TMEM:
+//   warp 0   TMA producer   (X tile 128 x 128B, Y tile BN x 128B per stage, SW128)
+//   warp 1   TMEM alloc + single-thread tcgen05.mma.kind::f8f6f4 issue (4 x K32 per stage)
+//   warps 2-5 epilogue      (tcgen05.ld 32x32b, scales, bias, cast, store)
+// Decode regime (M <= 128, weight-bandwidth bound): swap-AB -> the weight matrix is X
+// (128 weight rows per CTA) and the tokens are Y (BN = M rounded to 16..128), optional
+// split-K over gridDim.z with fp32 red.add into a caller workspace so all 148 SMs
+// stream weights even when N/128 < 148.  Large M: tokens on X, weights on Y, BN = 256.
+#include <cuda.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "umma.cuh"
+
+namespace b200 {
+
+constexpr int kGemmThreads = 192;
+constexpr int kBK = 128;  // bytes of K per stage = one swizzle span (128 fp8 elements)
+
+template <int BN> struct GemmCfg {
+  static constexpr int X_BYTES = 128 * kBK;
+  static constexpr int Y_BYTES = BN * kBK;
+  static constexpr int STAGE_BYTES = X_BYTES + Y_BYTES;
+  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+  static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+struct GemmArgs {
+  void* out;
+  const float* a_scales;  // per token (M) or [1]
+  const float* b_scales;  // per channel (N) or [1]
+  const void* bias;       // [N] out dtype or null
+  float* splitk_ws;       // fp32 [M][N] zero-initialised (split-K only)
+  int* splitk_cnt;        // per output tile arrival counters, zero-initialised
+  int64_t ldc;
+  int M, N, K;
+  int a_scales_numel, b_scales_numel;
+  int k_blocks_per_split;
+};
+
+template <typename OutT> __device__ __forceinline__ void store16(OutT* dst, const float (&v)[16], bool vec_ok);
+template <> __device__ __forceinline__ void store16<__nv_bfloat16>(__nv_bfloat16* dst, const float (&v)[16], bool vec_ok) {
+  if (vec_ok) {
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      __nv_bfloat162 p = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+      w[i] = *reinterpret_cast<uint32_t*>(&p);
+    }
+    reinterpret_cast<uint4*>(dst)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    reinterpret_cast<uint4*>(dst)[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) dst[i] = __float2bfloat16_rn(v[i]);
+  }
+}
+template <> __device__ __forceinline__ void store16<__half>(__half* dst, const float (&v)[16], bool vec_ok) {
+  if (vec_ok) {
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      __half2 p = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+      w[i] = *reinterpret_cast<uint32_t*>(&p);
+    }
+    reinterpret_cast<uint4*>(dst)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    reinterpret_cast<uint4*>(dst)[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) dst[i] = __float2half_rn(v[i]);
+  }
+}
+
+// X rows -> TMEM lanes (128 per CTA), Y rows -> TMEM columns (BN per CTA).
+// kSwap == false: X = A (tokens, M), Y = B (weights, N).  kSwap == true: X = B, Y = A.
+template <int BN, bool kSwap, typename OutT>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+    fp8_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_y,
+                    const GemmArgs g) {
+  using Cfg = GemmCfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int x0 = blockIdx.x * 128, y0 = blockIdx.y * BN;
+  const int total_kb = (g.K + kBK - 1) / kBK;
+  const int kb_begin = blockIdx.z * g.k_blocks_per_split;
+  const int kb_end = min(total_kb, kb_begin + g.k_blocks_per_split);
+  const int nkb = kb_end - kb_begin;  // host guarantees > 0
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+    prefetch_tensormap(&tmap_x);
+    prefetch_tensormap(&tmap_y);
+  }
+  if (warp == 1) umma::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (umma::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      // weights are streamed once (evict-first); the small token operand is re-read by every CTA (keep)
+      const uint64_t hint_x = kSwap ? kEvictFirst : kEvictLast;
+      const uint64_t hint_y = kSwap ? kEvictLast : kEvictFirst;
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sx = smem + stage * Cfg::STAGE_BYTES;
+        mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+        tma_load_2d(sx, &tmap_x, &full_bar[stage], kb * kBK, x0, hint_x);
+        tma_load_2d(sx + Cfg::X_BYTES, &tmap_y, &full_bar[stage], kb * kBK, y0, hint_y);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (umma::elect_one()) {
+      constexpr uint32_t idesc = umma::make_idesc_f8(128, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        umma::fence_after_sync();
+        const uint32_t sx = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+        const uint64_t dx = umma::make_desc_k_sw128(sx);
+        const uint64_t dy = umma::make_desc_k_sw128(sx + Cfg::X_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < kBK / 32; ++kk)
+          umma::mma_f8f6f4(tmem_base, umma::desc_advance(dx, kk * 32), umma::desc_advance(dy, kk * 32), idesc,
+                           (kb | kk) != 0);
+        umma::commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma::commit(tmem_full_bar);
+    }
+  } else {
+    // ===== epilogue: warp w owns TMEM lanes 32*(w%4) .. +31 =====
+    const int q = warp & 3;
+    const int xi = x0 + q * 32 + lane;  // X row of this thread
+    mbar_wait(tmem_full_bar, 0);
+    umma::fence_after_sync();
+    const int x_lim = kSwap ? g.N : g.M;
+    const int y_lim = kSwap ? g.M : g.N;
+    OutT* outp = reinterpret_cast<OutT*>(g.out);
+    const OutT* bias = reinterpret_cast<const OutT*>(g.bias);
+    const bool split = gridDim.z > 1;
+    // per-row (X side) scale and bias
+    float sx_row = 1.f, bias_row = 0.f;
+    if (xi < x_lim) {
+      if (kSwap) {
+        sx_row = g.b_scales[g.b_scales_numel > 1 ? xi : 0];
+        if (bias) bias_row = to_float(bias[xi]);
+      } else {
+        sx_row = g.a_scales[g.a_scales_numel > 1 ? xi : 0];
+      }
+    }
+#pragma unroll 1
+    for (int c = 0; c < BN; c += 16) {
+      uint32_t r[16];
+      umma::ld_32x32b_x16(tmem_base + ((uint32_t)(q * 32) << 16) + c, r);
+      umma::ld_wait();
+      if (xi >= x_lim || y0 + c >= y_lim) continue;
+      if (split) {
+        // accumulate raw fp32 partials; scaling happens in the finishing pass
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int yj = y0 + c + j;
+          if (yj < y_lim) {
+            const int64_t o = kSwap ? (int64_t)yj * g.N + xi : (int64_t)xi * g.N + yj;
+            atomicAdd(g.splitk_ws + o, __uint_as_float(r[j]));
+          }
+        }
+        continue;
+      }
+      float v[16];
+      if constexpr (kSwap) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int m = y0 + c + j;
+          if (m < g.M) {
+            const float as = g.a_scales[g.a_scales_numel > 1 ? m : 0];
+            outp[(int64_t)m * g.ldc + xi] = from_float<OutT>(__uint_as_float(r[j]) * as * sx_row + bias_row);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int n = y0 + c + j;  // N % 16 == 0 -> the whole chunk is in range
+          const float bs = g.b_scales[g.b_scales_numel > 1 ? n : 0];
+          v[j] = __uint_as_float(r[j]) * sx_row * bs + (bias ? to_float(bias[n]) : 0.f);
+        }
+        OutT* dst = outp + (int64_t)xi * g.ldc + y0 + c;
+        store16<OutT>(dst, v, (reinterpret_cast<uintptr_t>(dst) & 15) == 0);
+      }
+    }
+    if (split) {
+      // last CTA of this output tile converts the accumulated workspace and re-zeroes it
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // epilogue warps only
+      __shared__ int s_last;
+      if (threadIdx.x == 64) {
+        const int tile = blockIdx.y * gridDim.x + blockIdx.x;
+        const int prev = atomicAdd(g.splitk_cnt + tile, 1);
+        s_last = (prev == (int)gridDim.z - 1);
+        if (s_last) g.splitk_cnt[tile] = 0;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (s_last) {
+        __threadfence();
+        if (xi < x_lim) {
+          for (int j = 0; j < BN; ++j) {
+            const int yj = y0 + j;
+            if (yj >= y_lim) break;
+            const int m = kSwap ? yj : xi, n = kSwap ? xi : yj;
+            float* w = g.splitk_ws + (int64_t)m * g.N + n;
+            const float acc = __ldcg(w);
+            *w = 0.f;
+            const float as = g.a_scales[g.a_scales_numel > 1 ? m : 0];
+            const float bs = g.b_scales[g.b_scales_numel > 1 ? n : 0];
+            outp[(int64_t)m * g.ldc + n] = from_float<OutT>(acc * as * bs + (bias ? to_float(bias[n]) : 0.f));
+          }
+        }
+      }
+    }
+  }
+  umma::fence_before_sync();
+  __syncthreads();
+  if (warp == 1) umma::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+// ---- host side ------------------------------------------------------------------
+struct Tmap2Key {
+  const void* base;
+  int64_t ld;
+  int rows, k, box_rows, dt;
+  bool operator==(const Tmap2Key& o) const {
+    return base == o.base && ld == o.ld && rows == o.rows && k == o.k && box_rows == o.box_rows && dt == o.dt;
+  }
+};
+struct Tmap2Hash {
+  size_t operator()(const Tmap2Key& k) const {
+    size_t x = reinterpret_cast<size_t>(k.base);
+    auto mix = [&](uint64_t v) { x ^= v + 0x9e3779b97f4a7c15ull + (x << 6) + (x >> 2); };
+    mix(k.ld); mix(k.rows); mix(k.k); mix(k.box_rows); mix(k.dt);
+    return x;
+  }
+};
+// 2-D K-major operand [rows][k_bytes] (row pitch ld bytes), box = 128 bytes x box_rows, SW128.
+int get_kmajor_tmap(CUtensorMap* out, const void* base, int rows, int k_bytes, int64_t ld_bytes, int box_rows) {
+  static std::mutex mu;
+  static std::unordered_map<Tmap2Key, CUtensorMap, Tmap2Hash> cache;
+  Tmap2Key key{base, ld_bytes, rows, k_bytes, box_rows, 0};
+  std::lock_guard<std::mutex> lk(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) {
+    *out = it->second;
+    return 0;
+  }
+  uint64_t dims[2] = {(uint64_t)k_bytes, (uint64_t)rows};
+  uint64_t strides[1] = {(uint64_t)ld_bytes};
+  uint32_t box[2] = {128, (uint32_t)box_rows};
+  CUtensorMap tm;
+  int rc = encode_tmap(&tm, kTmaU8, 2, base, dims, strides, box, kSwizzle128);
+  if (rc) return rc;
+  if (cache.size() > 8192) cache.clear();
+  cache.emplace(key, tm);
+  *out = tm;
+  return 0;
+}
+
+template <int BN, bool kSwap, typename OutT>
+static int launch_fp8_gemm(const CUtensorMap& tx, const CUtensorMap& ty, const GemmArgs& g, dim3 grid,
+                           cudaStream_t stream) {
+  using Cfg = GemmCfg<BN>;
+  auto kern = fp8_gemm_kernel<BN, kSwap, OutT>;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) {
+      set_error("fp8 gemm: cudaFuncSetAttribute(%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
+      return B200_ERR_CUDA;
+    }
+    attr = true;
+  }
+  kern<<<grid, kGemmThreads, Cfg::SMEM_BYTES, stream>>>(tx, ty, g);
+  B200_CHECK_LAUNCH();
+  count_launch();
+  return 0;
+}
+
+template <typename OutT>
+static int run_fp8_gemm(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
+                        const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
+                        int a_scales_numel, int b_scales_numel, void* workspace, size_t workspace_bytes,
+                        cudaStream_t stream) {
+  GemmArgs g;
+  g.out = out;
+  g.a_scales = a_scales;
+  g.b_scales = b_scales;
+  g.bias = bias;
+  g.ldc = ldc;
+  g.M = M;
+  g.N = N;
+  g.K = K;
+  g.a_scales_numel = a_scales_numel;
+  g.b_scales_numel = b_scales_numel;
+  g.splitk_ws = nullptr;
+  g.splitk_cnt = nullptr;
+  const int total_kb = (K + kBK - 1) / kBK;
+  g.k_blocks_per_split = total_kb;
+  const bool swap = M <= 128;
+  CUtensorMap tx, ty;
+  int rc;
+  if (swap) {
+    const int bn = M <= 16 ? 16 : (M <= 32 ? 32 : (M <= 64 ? 64 : 128));
+    if ((rc = get_kmajor_tmap(&tx, b, N, K, ldb, 128))) return rc;
+    if ((rc = get_kmajor_tmap(&ty, a, M, K, lda, bn))) return rc;
+    const int tiles = (N + 127) / 128;
+    int splits = 1;
+    const size_t need = (size_t)M * N * 4 + (size_t)tiles * 4;
+    if (workspace && workspace_bytes >= need && tiles * 2 <= sm_count() && total_kb >= 8) {
+      splits = sm_count() / tiles;
+      if (splits > total_kb / 4) splits = total_kb / 4;
+      if (splits > 8) splits = 8;
+      if (splits < 1) splits = 1;
+    }
+    if (splits > 1) {
+      g.k_blocks_per_split = (total_kb + splits - 1) / splits;
+      splits = (total_kb + g.k_blocks_per_split - 1) / g.k_blocks_per_split;  // no empty split
+      g.splitk_ws = reinterpret_cast<float*>(workspace);
+      g.splitk_cnt = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(workspace) + (size_t)M * N * 4);
+    }
+    dim3 grid(tiles, 1, splits);
+    switch (bn) {
+      case 16: return launch_fp8_gemm<16, true, OutT>(tx, ty, g, grid, stream);
+      case 32: return launch_fp8_gemm<32, true, OutT>(tx, ty, g, grid, stream);
+      case 64: return launch_fp8_gemm<64, true, OutT>(tx, ty, g, grid, stream);
+      default: return launch_fp8_gemm<128, true, OutT>(tx, ty, g, grid, stream);
+    }
+  }
+  const int bn = (N % 256 == 0 || N > 2048) ? 256 : 128;
+  if ((rc = get_kmajor_tmap(&tx, a, M, K, lda, 128))) return rc;
+  if ((rc = get_kmajor_tmap(&ty, b, N, K, ldb, bn))) return rc;
+  dim3 grid((M + 127) / 128, (N + bn - 1) / bn, 1);
+  if (bn == 256) return launch_fp8_gemm<256, false, OutT>(tx, ty, g, grid, stream);
+  return launch_fp8_gemm<128, false, OutT>(tx, ty, g, grid, stream);
+}
+
+}  // namespace b200
+
+extern "C" size_t b200_scaled_mm_workspace_bytes(int M, int N) {
+  // fp32 split-K accumulator + one counter per 128-row weight tile; must be
+  // zero-initialised once by the caller (kernels leave it zeroed).
+  if (M > 128) return 0;
+  return (size_t)M * N * 4 + (size_t)((N + 127) / 128) * 4;
+}
+
+extern "C" int b200_scaled_mm_fp8(void* out, const void* a, const void* b, const float* a_scales,
+                                  const float* b_scales, const void* bias, int M, int N, int K, int64_t lda,
+                                  int64_t ldb, int64_t ldc, int a_scales_numel, int b_scales_numel, int out_dtype,
+                                  void* workspace, size_t workspace_bytes, b200_stream_t stream) {
+  using namespace b200;
+  B200_CHECK_ARG(M >= 0 && N > 0 && K > 0, B200_ERR_INVALID_ARG, "scaled_mm: bad sizes M=%d N=%d K=%d", M, N, K);
+  B200_CHECK_ARG(K % 16 == 0 && N % 16 == 0, B200_ERR_INVALID_ARG,
+                 "scaled_mm: b.shape[0] (K=%d) and b.shape[1] (N=%d) must be multiples of 16", K, N);
+  B200_CHECK_ARG(a_scales_numel == 1 || a_scales_numel == M, B200_ERR_INVALID_ARG,
+                 "scaled_mm: a_scales must have 1 or M=%d elements (got %d)", M, a_scales_numel);
+  B200_CHECK_ARG(b_scales_numel == 1 || b_scales_numel == N, B200_ERR_INVALID_ARG,
+                 "scaled_mm: b_scales must have 1 or N=%d elements (got %d)", N, b_scales_numel);
+  B200_CHECK_ARG(out_dtype == B200_DT_BF16 || out_dtype == B200_DT_F16, B200_ERR_INVALID_ARG,
+                 "scaled_mm: out dtype must be bf16 or fp16");
+  if (M == 0) return 0;
+  B200_CHECK_ARG(out && a && b && a_scales && b_scales, B200_ERR_INVALID_ARG, "scaled_mm: null pointer");
+  B200_CHECK_ARG(lda >= K && ldb >= K && ldc >= N, B200_ERR_INVALID_ARG, "scaled_mm: leading dimensions too small");
+  B200_CHECK_ARG(lda % 16 == 0 && ldb % 16 == 0 && reinterpret_cast<uintptr_t>(a) % 16 == 0 &&
+                     reinterpret_cast<uintptr_t>(b) % 16 == 0,
+                 B200_ERR_ALIGNMENT, "scaled_mm: a and b must be 16-byte aligned with row pitches multiple of 16");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (out_dtype == B200_DT_BF16)
+    return run_fp8_gemm<__nv_bfloat16>(out, a, b, a_scales, b_scales, bias, M, N, K, lda, ldb, ldc, a_scales_numel,
+                                       b_scales_numel, workspace, workspace_bytes, s);
+  return run_fp8_gemm<__half>(out, a, b, a_scales, b_scales, bias, M, N, K, lda, ldb, ldc, a_scales_numel,
+                              b_scales_numel, workspace, workspace_bytes, s);
+}

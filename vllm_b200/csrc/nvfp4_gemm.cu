@@ -1,0 +1,301 @@
+// NVFP4 block-scaled GEMM on tcgen05:  out = alpha * (A4 . SFA) @ (B4 . SFB)^T.
+// Reference semantics: cutlass_scaled_fp4_mm, csrc/libtorch_stable/quantization/fp4/
+// nvfp4_scaled_mm_entry.cu:41-69, nvfp4_scaled_mm_kernels.cu:46-137 (Fp4GemmSm100 configs),
+// :214-248 (M dispatch), :279-347 (shape checks); SF layout nvfp4_utils.cuh:168-199.
+//
+// B200 design: same warp-specialised skeleton as fp8_gemm.cu.  Operands are packed
+// e2m1 (2 per byte), K-major, one 128-byte swizzle span = 256 K-elements per stage;
+// tcgen05.mma.kind::mxf4nvf4.block_scale.block16 consumes K=64 per instruction.  The
+// e4m3 scale factors already sit in global memory in the tensor-core 128x4 atom order
+// ([rowTile][kTile][32][4][4] = 512 B per atom), so a stage's 4 atoms are one
+// contiguous 2 KB cp.async.bulk; tcgen05.cp.32x128b.warpx4 moves each atom into 4 TMEM
+// columns (double-buffered by stage parity) right before the MMA that reads it.
+#include <cuda.h>
+
+#include "umma.cuh"
+
+namespace b200 {
+
+int get_kmajor_tmap(CUtensorMap* out, const void* base, int rows, int k_bytes, int64_t ld_bytes, int box_rows);
+
+constexpr int kF4Threads = 192;
+constexpr int kF4BK = 128;       // bytes per stage along K (256 e2m1)
+constexpr int kAtomBytes = 512;  // 128 rows x 4 scale factors
+
+template <int BN> struct F4Cfg {
+  static constexpr int X_BYTES = 128 * kF4BK;
+  static constexpr int Y_BYTES = BN * kF4BK;
+  static constexpr int YT = (BN + 127) / 128;           // 128-row SF tiles on the Y side
+  static constexpr int SFX_BYTES = 4 * kAtomBytes;      // 4 k-atoms
+  static constexpr int SFY_BYTES = YT * 4 * kAtomBytes;
+  static constexpr int STAGE_BYTES = X_BYTES + Y_BYTES + SFX_BYTES + SFY_BYTES;
+  static constexpr int STAGES = (196 * 1024) / STAGE_BYTES > 8 ? 8 : (196 * 1024) / STAGE_BYTES;
+  static constexpr int ACC_COLS = BN < 32 ? 32 : BN;
+  static constexpr int SF_COLS = 16 + 16 * YT;  // per parity buffer
+  static constexpr int NEED_COLS = ACC_COLS + 2 * SF_COLS;
+  static constexpr int TMEM_COLS = NEED_COLS <= 128 ? 128 : (NEED_COLS <= 256 ? 256 : 512);
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+};
+
+struct F4Args {
+  void* out;
+  const uint8_t* sfx;  // SF of the X-side operand (swizzled atoms)
+  const uint8_t* sfy;
+  const float* alpha;
+  int64_t ldc;
+  int M, N, K;
+  int num_k_atoms;  // ceil(K / 64)
+};
+
+__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// SWIZZLE_NONE K-major descriptor over one 512-byte SF atom: 8-row x 16-byte core
+// matrices stacked every 128 bytes (SBO), single core matrix along K (LBO unused).
+__device__ __forceinline__ uint64_t make_sf_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(128 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+
+template <int BN, bool kSwap, typename OutT>
+__global__ void __launch_bounds__(kF4Threads, 1)
+    nvfp4_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_y,
+                      const F4Args g) {
+  using Cfg = F4Cfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int x0 = blockIdx.x * 128, y0 = blockIdx.y * BN;
+  const int k_bytes = g.K / 2;
+  const int nkb = (k_bytes + kF4BK - 1) / kF4BK;
+  const int y_rows = kSwap ? g.M : g.N;
+  const int y_tiles_total = (y_rows + 127) / 128;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+    prefetch_tensormap(&tmap_x);
+    prefetch_tensormap(&tmap_y);
+  }
+  if (warp == 1) umma::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (umma::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint64_t hint_x = kSwap ? kEvictFirst : kEvictLast;
+      const uint64_t hint_y = kSwap ? kEvictLast : kEvictFirst;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sx = smem + stage * Cfg::STAGE_BYTES;
+        uint8_t* sy = sx + Cfg::X_BYTES;
+        uint8_t* ssfx = sy + Cfg::Y_BYTES;
+        uint8_t* ssfy = ssfx + Cfg::SFX_BYTES;
+        const int atoms = min(4, g.num_k_atoms - 4 * kb);
+        int yt_live = 0;
+#pragma unroll
+        for (int t = 0; t < Cfg::YT; ++t) yt_live += (blockIdx.y * Cfg::YT + t) < y_tiles_total ? 1 : 0;
+        const uint32_t bytes = Cfg::X_BYTES + Cfg::Y_BYTES + (uint32_t)atoms * kAtomBytes * (1 + yt_live);
+        mbar_arrive_expect_tx(&full_bar[stage], bytes);
+        tma_load_2d(sx, &tmap_x, &full_bar[stage], kb * kF4BK, x0, hint_x);
+        tma_load_2d(sy, &tmap_y, &full_bar[stage], kb * kF4BK, y0, hint_y);
+        bulk_load_1d(ssfx, g.sfx + ((int64_t)blockIdx.x * g.num_k_atoms + 4 * kb) * kAtomBytes, atoms * kAtomBytes,
+                     &full_bar[stage]);
+#pragma unroll
+        for (int t = 0; t < Cfg::YT; ++t) {
+          const int yt = blockIdx.y * Cfg::YT + t;
+          if (yt < y_tiles_total)
+            bulk_load_1d(ssfy + t * 4 * kAtomBytes, g.sfy + ((int64_t)yt * g.num_k_atoms + 4 * kb) * kAtomBytes,
+                         atoms * kAtomBytes, &full_bar[stage]);
+        }
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (umma::elect_one()) {
+      constexpr uint32_t idesc = umma::make_idesc_nvf4(128, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < nkb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        umma::fence_after_sync();
+        const uint32_t sx = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+        const uint32_t sy = sx + Cfg::X_BYTES;
+        const uint32_t ssfx = sy + Cfg::Y_BYTES;
+        const uint32_t ssfy = ssfx + Cfg::SFX_BYTES;
+        const uint64_t dx = umma::make_desc_k_sw128(sx);
+        const uint64_t dy = umma::make_desc_k_sw128(sy);
+        const uint32_t t_sfx = tmem_base + Cfg::ACC_COLS + (kb & 1) * Cfg::SF_COLS;
+        const uint32_t t_sfy = t_sfx + 16;
+        const int atoms = min(4, g.num_k_atoms - 4 * kb);
+        for (int kk = 0; kk < atoms; ++kk) {
+          umma::cp_32x128b_warpx4(t_sfx + 4 * kk, make_sf_desc(ssfx + kk * kAtomBytes));
+#pragma unroll
+          for (int t = 0; t < Cfg::YT; ++t)
+            umma::cp_32x128b_warpx4(t_sfy + 4 * Cfg::YT * kk + 4 * t,
+                                    make_sf_desc(ssfy + t * 4 * kAtomBytes + kk * kAtomBytes));
+          umma::mma_nvf4_block16(tmem_base, umma::desc_advance(dx, kk * 32), umma::desc_advance(dy, kk * 32), idesc,
+                                 (kb | kk) != 0, t_sfx + 4 * kk, t_sfy + 4 * Cfg::YT * kk);
+        }
+        umma::commit(&empty_bar[stage]);
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma::commit(tmem_full_bar);
+    }
+  } else {
+    const int q = warp & 3;
+    const int xi = x0 + q * 32 + lane;
+    mbar_wait(tmem_full_bar, 0);
+    umma::fence_after_sync();
+    const int x_lim = kSwap ? g.N : g.M;
+    const int y_lim = kSwap ? g.M : g.N;
+    OutT* outp = reinterpret_cast<OutT*>(g.out);
+    const float alpha = *g.alpha;
+#pragma unroll 1
+    for (int c = 0; c < BN; c += 16) {
+      uint32_t r[16];
+      umma::ld_32x32b_x16(tmem_base + ((uint32_t)(q * 32) << 16) + c, r);
+      umma::ld_wait();
+      if (xi >= x_lim || y0 + c >= y_lim) continue;
+      if constexpr (kSwap) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int m = y0 + c + j;
+          if (m < g.M) outp[(int64_t)m * g.ldc + xi] = from_float<OutT>(__uint_as_float(r[j]) * alpha);
+        }
+      } else {
+        OutT* dst = outp + (int64_t)xi * g.ldc + y0 + c;
+        if (y0 + c + 16 <= y_lim && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+          uint32_t w[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if constexpr (std::is_same<OutT, __nv_bfloat16>::value) {
+              __nv_bfloat162 p =
+                  __floats2bfloat162_rn(__uint_as_float(r[2 * i]) * alpha, __uint_as_float(r[2 * i + 1]) * alpha);
+              w[i] = *reinterpret_cast<uint32_t*>(&p);
+            } else {
+              __half2 p = __floats2half2_rn(__uint_as_float(r[2 * i]) * alpha, __uint_as_float(r[2 * i + 1]) * alpha);
+              w[i] = *reinterpret_cast<uint32_t*>(&p);
+            }
+          }
+          reinterpret_cast<uint4*>(dst)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+          reinterpret_cast<uint4*>(dst)[1] = make_uint4(w[4], w[5], w[6], w[7]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (y0 + c + j < y_lim) dst[j] = from_float<OutT>(__uint_as_float(r[j]) * alpha);
+        }
+      }
+    }
+  }
+  umma::fence_before_sync();
+  __syncthreads();
+  if (warp == 1) umma::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+template <int BN, bool kSwap, typename OutT>
+static int launch_f4(const CUtensorMap& tx, const CUtensorMap& ty, const F4Args& g, dim3 grid, cudaStream_t stream) {
+  using Cfg = F4Cfg<BN>;
+  auto kern = nvfp4_gemm_kernel<BN, kSwap, OutT>;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) {
+      set_error("nvfp4 gemm: cudaFuncSetAttribute(%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
+      return B200_ERR_CUDA;
+    }
+    attr = true;
+  }
+  kern<<<grid, kF4Threads, Cfg::SMEM_BYTES, stream>>>(tx, ty, g);
+  B200_CHECK_LAUNCH();
+  count_launch();
+  return 0;
+}
+
+template <typename OutT>
+static int run_f4(void* out, const void* a, const void* b, const void* sfa, const void* sfb, const float* alpha,
+                  int M, int N, int K, int64_t ldc, cudaStream_t stream) {
+  F4Args g;
+  g.out = out;
+  g.alpha = alpha;
+  g.ldc = ldc;
+  g.M = M;
+  g.N = N;
+  g.K = K;
+  g.num_k_atoms = (K + 63) / 64;
+  CUtensorMap tx, ty;
+  int rc;
+  const int kb = K / 2;
+  if (M <= 128) {
+    const int bn = M <= 16 ? 16 : (M <= 32 ? 32 : (M <= 64 ? 64 : 128));
+    g.sfx = reinterpret_cast<const uint8_t*>(sfb);
+    g.sfy = reinterpret_cast<const uint8_t*>(sfa);
+    if ((rc = get_kmajor_tmap(&tx, b, N, kb, kb, 128))) return rc;
+    if ((rc = get_kmajor_tmap(&ty, a, M, kb, kb, bn))) return rc;
+    dim3 grid((N + 127) / 128, 1, 1);
+    switch (bn) {
+      case 16: return launch_f4<16, true, OutT>(tx, ty, g, grid, stream);
+      case 32: return launch_f4<32, true, OutT>(tx, ty, g, grid, stream);
+      case 64: return launch_f4<64, true, OutT>(tx, ty, g, grid, stream);
+      default: return launch_f4<128, true, OutT>(tx, ty, g, grid, stream);
+    }
+  }
+  g.sfx = reinterpret_cast<const uint8_t*>(sfa);
+  g.sfy = reinterpret_cast<const uint8_t*>(sfb);
+  const int bn = N >= 2048 ? 256 : 128;
+  if ((rc = get_kmajor_tmap(&tx, a, M, kb, kb, 128))) return rc;
+  if ((rc = get_kmajor_tmap(&ty, b, N, kb, kb, bn))) return rc;
+  dim3 grid((M + 127) / 128, (N + bn - 1) / bn, 1);
+  if (bn == 256) return launch_f4<256, false, OutT>(tx, ty, g, grid, stream);
+  return launch_f4<128, false, OutT>(tx, ty, g, grid, stream);
+}
+
+}  // namespace b200
+
+extern "C" int b200_scaled_mm_nvfp4(void* out, const void* a, const void* b, const void* sfa, const void* sfb,
+                                    const float* alpha, int M, int N, int K, int64_t ldc, int out_dtype,
+                                    b200_stream_t stream) {
+  using namespace b200;
+  B200_CHECK_ARG(M >= 0 && N > 0 && K > 0, B200_ERR_INVALID_ARG, "scaled_fp4_mm: bad sizes M=%d N=%d K=%d", M, N, K);
+  B200_CHECK_ARG(K % 32 == 0, B200_ERR_INVALID_ARG, "Expected k to be divisible by 32, but got a shape: (%d, %d)", M,
+                 K / 2);
+  B200_CHECK_ARG(N % 32 == 0, B200_ERR_INVALID_ARG, "Expected n to be divisible by 32, but got b shape: (%d, %d)", N,
+                 K / 2);
+  B200_CHECK_ARG(out_dtype == B200_DT_BF16 || out_dtype == B200_DT_F16, B200_ERR_INVALID_ARG,
+                 "Unsupported output data type of nvfp4 mm");
+  if (M == 0) return 0;
+  B200_CHECK_ARG(out && a && b && sfa && sfb && alpha, B200_ERR_INVALID_ARG, "scaled_fp4_mm: null pointer");
+  B200_CHECK_ARG(ldc >= N, B200_ERR_INVALID_ARG, "scaled_fp4_mm: ldc too small");
+  B200_CHECK_ARG(reinterpret_cast<uintptr_t>(a) % 16 == 0 && reinterpret_cast<uintptr_t>(b) % 16 == 0 &&
+                     reinterpret_cast<uintptr_t>(sfa) % 16 == 0 && reinterpret_cast<uintptr_t>(sfb) % 16 == 0,
+                 B200_ERR_ALIGNMENT, "scaled_fp4_mm: operands and scale factors must be 16-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (out_dtype == B200_DT_BF16) return run_f4<__nv_bfloat16>(out, a, b, sfa, sfb, alpha, M, N, K, ldc, s);
+  return run_f4<__half>(out, a, b, sfa, sfb, alpha, M, N, K, ldc, s);
+}

@@ -1,0 +1,696 @@
+// Paged-attention decode for sm_100a: split-KV + combine, GQA-grouped.
+//
+// Reference semantics: legacy paged_attention_v1/v2 (vllm/_custom_ops.py:120-163,
+// docs/design/paged_attention.md, ROCm port csrc/rocm/attention.cu:320-1520) and the
+// in-tree successor kernel_unified_attention 3D + reduce_segments
+// (vllm/v1/attention/ops/triton_unified_attention.py:179-681,685-771).
+//
+// B200 design (HBM-bound):
+//  * one CTA per (split, kv-head[, q-head group of 16], sequence); the G = Hq/Hkv
+//    query heads of a kv-head share every K/V byte, so KV is read once (the
+//    legacy kernel re-read it G times);
+//  * K/V pages are gathered with TMA (cp.async.bulk.tensor.4d over the
+//    [D, H, block_size, num_blocks] view of the cache with its true strides, so
+//    NHD / HND / K|V-interleaved layouts all work) into 128B-swizzled shared
+//    memory; each of the 4 warps owns a private ring of slots and mbarriers and
+//    re-arms a slot as soon as it has consumed it -> no block-wide barrier in the
+//    main loop, 12-16 page-chunks in flight per CTA, 2-3 CTAs per SM;
+//  * QK^T and PV for the (<=16) grouped heads run on mma.sync m16n8k16 with fp32
+//    accumulation: the kernel is bandwidth bound, the tensor pipe is mostly idle;
+//  * online softmax in the exp2 domain, quad shuffles for row max / row sum,
+//    warps merged through shared memory at the end, split partials merged by a
+//    second tiny kernel.
+#include <cuda.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr int kChunk = 16;  // tokens per TMA box (block_size must be a multiple)
+constexpr int kWarps = 4;   // consumer warps per CTA
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+template <int D, int KV> struct DecodeCfg {
+  static constexpr int ES = (KV == B200_KV_AUTO) ? 2 : 1;  // bytes per cache element
+  static constexpr int ROWB = D * ES;                      // bytes per (token, head) row
+  static_assert(ROWB % 128 == 0, "row must be a whole number of 128-byte swizzle spans");
+  static constexpr int NSUB = ROWB / 128;           // TMA boxes per K (or V) chunk
+  static constexpr int SUB_BYTES = kChunk * 128;    // 2 KB, 1024-aligned
+  static constexpr int KCH_BYTES = NSUB * SUB_BYTES;
+  static constexpr int SLOT_BYTES = 2 * KCH_BYTES;  // K chunk + V chunk
+  static constexpr int NSLOT = ROWB >= 512 ? 2 : (ROWB == 256 ? 3 : 4);
+  static constexpr int RING_BYTES = kWarps * NSLOT * SLOT_BYTES;
+  static constexpr int OPAD = D + 8;  // fp32 row pitch of the merge buffer
+  static constexpr int EPI_BYTES = kWarps * 16 * OPAD * 4 + 2 * kWarps * 16 * 4;
+  static constexpr int BAR_BYTES = kWarps * NSLOT * 8;
+  static constexpr int SMEM_BYTES = (RING_BYTES > EPI_BYTES ? RING_BYTES : EPI_BYTES) + BAR_BYTES + 1024;
+  static constexpr int BOX_D = 128 / ES;  // elements per 128-byte span
+};
+
+struct DecodeArgs {
+  void* out;
+  const void* query;
+  const int32_t* block_table;
+  const int32_t* seq_lens;
+  const float* k_scale;
+  const float* v_scale;
+  float* out_lse;
+  float* part_o;   // [seq][hq][split][D]
+  float2* part_ml; // [seq][hq][split]
+  int64_t q_stride_seq, q_stride_head, out_stride_seq, out_stride_head, block_table_stride;
+  int num_q_heads, num_kv_heads, group, qgroups;  // group = Hq/Hkv, qgroups = ceil(group/16)
+  int block_size, num_splits, sliding_window;
+  float scale, soft_cap;
+};
+
+__device__ __forceinline__ uint32_t pack2(float a, float b, __nv_bfloat16) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ uint32_t pack2(float a, float b, __half) {
+  __half2 v = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+// two fp8 bytes (low 16 bits of x) -> packed f16x2, exact
+template <int KV> __device__ __forceinline__ uint32_t fp8x2_to_h2(uint32_t x) {
+  uint32_t r;
+  if constexpr (KV == B200_KV_FP8_E5M2) {
+    asm("{\n\t.reg .b16 lo;\n\tcvt.u16.u32 lo, %1;\n\tcvt.rn.f16x2.e5m2x2 %0, lo;\n\t}" : "=r"(r) : "r"(x));
+  } else {
+    asm("{\n\t.reg .b16 lo;\n\tcvt.u16.u32 lo, %1;\n\tcvt.rn.f16x2.e4m3x2 %0, lo;\n\t}" : "=r"(r) : "r"(x));
+  }
+  return r;
+}
+__device__ __forceinline__ float fast_tanh(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <typename QT> __device__ __forceinline__ uint32_t load_q_pair_as_half(const QT* p) {
+  // fp8-KV path runs the MMAs in f16 (e4m3/e5m2 are exactly representable);
+  // bf16 queries are converted with saturation to the f16 range.
+  if constexpr (std::is_same<QT, __half>::value) {
+    return *reinterpret_cast<const uint32_t*>(p);
+  } else {
+    __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(p);
+    float2 f = __bfloat1622float2(v);
+    f.x = fminf(fmaxf(f.x, -65504.f), 65504.f);
+    f.y = fminf(fmaxf(f.y, -65504.f), 65504.f);
+    __half2 h = __floats2half2_rn(f.x, f.y);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+}
+
+template <int SMEM> struct OccFor {
+  static constexpr int value = SMEM <= 74 * 1024 ? 3 : (SMEM <= 112 * 1024 ? 2 : 1);
+};
+
+template <typename QT, int D, int KV>
+__global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYTES>::value)
+    paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_v,
+                        const DecodeArgs a) {
+  using Cfg = DecodeCfg<D, KV>;
+  constexpr bool kFp8 = (KV != B200_KV_AUTO);
+  using MT = typename std::conditional<kFp8, __half, QT>::type;  // MMA operand type
+  constexpr bool kBf16 = std::is_same<MT, __nv_bfloat16>::value;
+  constexpr int NSLOT = Cfg::NSLOT;
+  constexpr int SUB = Cfg::SUB_BYTES;
+  constexpr int KS = D / 16;  // k-steps of QK^T == 16-wide d groups of PV
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  constexpr int kDataBytes = Cfg::RING_BYTES > Cfg::EPI_BYTES ? Cfg::RING_BYTES : Cfg::EPI_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kDataBytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int split = blockIdx.x, seq = blockIdx.z;
+  const int kvh = blockIdx.y / a.qgroups, qg = blockIdx.y - kvh * a.qgroups;
+  const int rows = min(16, a.group - qg * 16);  // live query heads of this CTA
+  const int qh0 = kvh * a.group + qg * 16;
+  const int len = a.seq_lens[seq];
+  const int lo = (a.sliding_window > 0) ? max(0, len - a.sliding_window) : 0;
+  const int c_begin = lo / kChunk, c_end = (len + kChunk - 1) / kChunk;
+  const int nc = max(0, c_end - c_begin);
+  int cps = (nc + a.num_splits - 1) / a.num_splits;
+  cps = (cps + kWarps - 1) / kWarps * kWarps;
+  const int c0 = c_begin + split * cps;
+  const int c1 = min(c_end, c0 + cps);
+
+  if (c0 >= c1) {  // nothing to attend to in this split
+    if (a.num_splits > 1) {
+      if ((int)threadIdx.x < rows)
+        a.part_ml[((int64_t)seq * a.num_q_heads + qh0 + threadIdx.x) * a.num_splits + split] =
+            make_float2(-INFINITY, 0.f);
+    } else {
+      QT* o = reinterpret_cast<QT*>(a.out) + (int64_t)seq * a.out_stride_seq + (int64_t)qh0 * a.out_stride_head;
+      for (int i = threadIdx.x; i < rows * D; i += blockDim.x)
+        o[(int64_t)(i / D) * a.out_stride_head + (i % D)] = from_float<QT>(0.f);
+      if (a.out_lse && (int)threadIdx.x < rows)
+        a.out_lse[(int64_t)seq * a.num_q_heads + qh0 + threadIdx.x] = -INFINITY;
+    }
+    return;
+  }
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kWarps * NSLOT; ++i) mbar_init(&bars[i], 1);
+    fence_barrier_init();
+    prefetch_tensormap(&tmap_k);
+    prefetch_tensormap(&tmap_v);
+  }
+  __syncthreads();
+
+  // ---- Q fragments (A operand, rows = query heads of the group) -------------
+  uint32_t qa[KS][4];
+  {
+    const QT* qb = reinterpret_cast<const QT*>(a.query) + (int64_t)seq * a.q_stride_seq +
+                   (int64_t)qh0 * a.q_stride_head;
+    const QT* q_lo = qb + (int64_t)g * a.q_stride_head;
+    const QT* q_hi = qb + (int64_t)(g + 8) * a.q_stride_head;
+    const bool v_lo = g < rows, v_hi = (g + 8) < rows;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      // fp8 path: MMA k-slots (2t,2t+1 | 2t+8,2t+9) map to d = 16ks+4t+(0,1 | 2,3)
+      const int ca = kFp8 ? 16 * ks + 4 * t : 16 * ks + 2 * t;
+      const int cb = kFp8 ? ca + 2 : ca + 8;
+      if constexpr (kFp8) {
+        qa[ks][0] = v_lo ? load_q_pair_as_half(q_lo + ca) : 0u;
+        qa[ks][1] = v_hi ? load_q_pair_as_half(q_hi + ca) : 0u;
+        qa[ks][2] = v_lo ? load_q_pair_as_half(q_lo + cb) : 0u;
+        qa[ks][3] = v_hi ? load_q_pair_as_half(q_hi + cb) : 0u;
+      } else {
+        qa[ks][0] = v_lo ? *reinterpret_cast<const uint32_t*>(q_lo + ca) : 0u;
+        qa[ks][1] = v_hi ? *reinterpret_cast<const uint32_t*>(q_hi + ca) : 0u;
+        qa[ks][2] = v_lo ? *reinterpret_cast<const uint32_t*>(q_lo + cb) : 0u;
+        qa[ks][3] = v_hi ? *reinterpret_cast<const uint32_t*>(q_hi + cb) : 0u;
+      }
+    }
+  }
+
+  const float kscale = (kFp8 && a.k_scale) ? *a.k_scale : 1.f;
+  const float sc_nat = a.scale * kscale;  // natural-domain logit scale
+  const float sc = sc_nat * kLog2e;       // exp2-domain logit scale
+  const bool use_cap = a.soft_cap > 0.f;
+  const float cap_inv = use_cap ? 1.f / a.soft_cap : 0.f;
+  const float cap_l2 = a.soft_cap * kLog2e;
+
+  // ---- per-warp chunk list, block ids prefetched 32 at a time -----------------
+  const int span = c1 - c0;
+  const int n_my = span > warp ? (span - warp + kWarps - 1) / kWarps : 0;
+  uint8_t* ring = smem + warp * NSLOT * Cfg::SLOT_BYTES;
+  uint64_t* wbar = bars + warp * NSLOT;
+  const int32_t* bt_row = a.block_table + (int64_t)seq * a.block_table_stride;
+  auto load_ids = [&](int batch) -> int {
+    const int i = batch * 32 + lane;
+    if (i < n_my) return bt_row[((c0 + warp + kWarps * i) * kChunk) / a.block_size];
+    return 0;
+  };
+  int ids_cur = load_ids(0), ids_next = load_ids(1), issue_batch = 0;
+  auto issue = [&](int ii, int slot) {
+    const int b = ii >> 5;
+    if (b != issue_batch) {
+      ids_cur = ids_next;
+      ids_next = load_ids(b + 1);
+      issue_batch = b;
+    }
+    const int blk = __shfl_sync(0xffffffffu, ids_cur, ii & 31);
+    if (lane == 0) {
+      const int c = c0 + warp + kWarps * ii;
+      const int tok_in_blk = (c * kChunk) % a.block_size;
+      uint8_t* dst = ring + slot * Cfg::SLOT_BYTES;
+      mbar_arrive_expect_tx(&wbar[slot], Cfg::SLOT_BYTES);
+#pragma unroll
+      for (int s = 0; s < Cfg::NSUB; ++s)
+        tma_load_4d(dst + s * SUB, &tmap_k, &wbar[slot], s * Cfg::BOX_D, kvh, tok_in_blk, blk, kEvictFirst);
+#pragma unroll
+      for (int s = 0; s < Cfg::NSUB; ++s)
+        tma_load_4d(dst + Cfg::KCH_BYTES + s * SUB, &tmap_v, &wbar[slot], s * Cfg::BOX_D, kvh, tok_in_blk, blk,
+                    kEvictFirst);
+    }
+  };
+  {
+    const int pre = min(NSLOT, n_my);
+    for (int ii = 0; ii < pre; ++ii) issue(ii, ii);
+  }
+
+  // ---- online-softmax state -------------------------------------------------
+  float o[2 * KS][4];
+#pragma unroll
+  for (int n = 0; n < 2 * KS; ++n) o[n][0] = o[n][1] = o[n][2] = o[n][3] = 0.f;
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;  // rows g and g+8
+
+  // per-lane ldmatrix address pieces
+  const int li = lane >> 3, lr = lane & 7;
+  // 16-bit KV:  K matrices (tok-lo,d-lo)(tok-lo,d-hi)(tok-hi,d-lo)(tok-hi,d-hi); V.trans (tok-lo,d)(tok-hi,d)(tok-lo,d+1)(tok-hi,d+1)
+  // fp8 KV:     K and V both (tok-lo,c)(tok-hi,c)(tok-lo,c+1)(tok-hi,c+1) with c = 16-byte column
+  const int k_tok = kFp8 ? ((li & 1) << 3) + lr : ((li >> 1) << 3) + lr;
+  const int k_cof = kFp8 ? (li >> 1) : (li & 1);
+  const int v_tok = ((li & 1) << 3) + lr;
+  const int v_cof = li >> 1;
+
+  int slot = 0;
+  uint32_t phase = 0;
+  for (int i = 0; i < n_my; ++i) {
+    const int c = c0 + warp + kWarps * i;
+    const uint32_t kbase = smem_u32(ring + slot * Cfg::SLOT_BYTES);
+    const uint32_t vbase = kbase + Cfg::KCH_BYTES;
+    mbar_wait(&wbar[slot], phase);
+
+    const int tok0 = c * kChunk;
+    if (tok0 + kChunk > len) {
+      // boundary chunk: rows past seq_len may hold stale/garbage bytes; p is 0
+      // there but 0 * NaN would poison the accumulator, so clear V rows.
+      const int valid = len - tok0;
+      uint8_t* vs = ring + slot * Cfg::SLOT_BYTES + Cfg::KCH_BYTES;
+      for (int idx = lane; idx < (kChunk - valid) * Cfg::NSUB * 8; idx += 32) {
+        const int row = valid + idx / (Cfg::NSUB * 8);
+        const int rem = idx % (Cfg::NSUB * 8);
+        *reinterpret_cast<uint4*>(vs + (rem >> 3) * SUB + row * 128 + (rem & 7) * 16) = make_uint4(0, 0, 0, 0);
+      }
+      __syncwarp();
+    }
+
+    // ---- S = Q K^T (16 x 16 tokens) ---------------------------------------
+    float s[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+    if constexpr (!kFp8) {
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+        const int dch = 2 * ks + k_cof;
+        uint32_t b[4];
+        ldmatrix_x4(b, kbase + (dch >> 3) * SUB + k_tok * 128 + (((dch & 7) ^ lr) << 4));
+        mma_16816<kBf16>(s[0], qa[ks], b[0], b[1]);
+        mma_16816<kBf16>(s[1], qa[ks], b[2], b[3]);
+      }
+    } else {
+#pragma unroll
+      for (int jj = 0; jj < KS / 2; ++jj) {
+        const int dch = 2 * jj + k_cof;  // 16-byte column = one k-step of 16 fp8
+        uint32_t b[4];
+        ldmatrix_x4(b, kbase + (dch >> 3) * SUB + k_tok * 128 + (((dch & 7) ^ lr) << 4));
+        mma_16816<false>(s[0], qa[2 * jj], fp8x2_to_h2<KV>(b[0]), fp8x2_to_h2<KV>(b[0] >> 16));
+        mma_16816<false>(s[1], qa[2 * jj], fp8x2_to_h2<KV>(b[1]), fp8x2_to_h2<KV>(b[1] >> 16));
+        mma_16816<false>(s[0], qa[2 * jj + 1], fp8x2_to_h2<KV>(b[2]), fp8x2_to_h2<KV>(b[2] >> 16));
+        mma_16816<false>(s[1], qa[2 * jj + 1], fp8x2_to_h2<KV>(b[3]), fp8x2_to_h2<KV>(b[3] >> 16));
+      }
+    }
+
+    // ---- scale, soft-cap, mask ------------------------------------------------
+    const bool need_mask = (tok0 + kChunk > len) || (tok0 < lo);
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float v = use_cap ? cap_l2 * fast_tanh(s[nt][e] * sc_nat * cap_inv) : s[nt][e] * sc;
+        if (need_mask) {
+          const int tok = tok0 + nt * 8 + 2 * t + (e & 1);
+          if (tok >= len || tok < lo) v = -INFINITY;
+        }
+        s[nt][e] = v;
+      }
+    float mx0 = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
+    float mx1 = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+    const float ms0 = (mn0 == -INFINITY) ? 0.f : mn0, ms1 = (mn1 == -INFINITY) ? 0.f : mn1;
+    const float al0 = fast_exp2(m0 - ms0), al1 = fast_exp2(m1 - ms1);
+    m0 = mn0;
+    m1 = mn1;
+    float p[2][4];
+#pragma unroll
+    for (int nt = 0; nt < 2; ++nt) {
+      p[nt][0] = fast_exp2(s[nt][0] - ms0);
+      p[nt][1] = fast_exp2(s[nt][1] - ms0);
+      p[nt][2] = fast_exp2(s[nt][2] - ms1);
+      p[nt][3] = fast_exp2(s[nt][3] - ms1);
+    }
+    l0 = l0 * al0 + (p[0][0] + p[0][1] + p[1][0] + p[1][1]);
+    l1 = l1 * al1 + (p[0][2] + p[0][3] + p[1][2] + p[1][3]);
+    if (__any_sync(0xffffffffu, (al0 != 1.f) || (al1 != 1.f))) {
+#pragma unroll
+      for (int n = 0; n < 2 * KS; ++n) {
+        o[n][0] *= al0;
+        o[n][1] *= al0;
+        o[n][2] *= al1;
+        o[n][3] *= al1;
+      }
+    }
+    uint32_t pa[4];
+    pa[0] = pack2(p[0][0], p[0][1], MT());
+    pa[1] = pack2(p[0][2], p[0][3], MT());
+    pa[2] = pack2(p[1][0], p[1][1], MT());
+    pa[3] = pack2(p[1][2], p[1][3], MT());
+
+    // ---- O += P V -----------------------------------------------------------
+    if constexpr (!kFp8) {
+#pragma unroll
+      for (int j = 0; j < KS; ++j) {
+        const int dch = 2 * j + v_cof;
+        uint32_t b[4];
+        ldmatrix_x4_trans(b, vbase + (dch >> 3) * SUB + v_tok * 128 + (((dch & 7) ^ lr) << 4));
+        mma_16816<kBf16>(o[2 * j], pa, b[0], b[1]);
+        mma_16816<kBf16>(o[2 * j + 1], pa, b[2], b[3]);
+      }
+    } else {
+      // One transposed 8x8(b16) matrix = 8 tokens x 16 fp8 columns.  After the
+      // transpose a thread holds tokens (2t, 2t+1) x columns (2g, 2g+1); the even
+      // / odd column of every pair feeds a separate n-tile (d = 16c + 2n + par).
+#pragma unroll
+      for (int jj = 0; jj < KS / 2; ++jj) {
+        const int dch = 2 * jj + v_cof;
+        uint32_t b[4];
+        ldmatrix_x4_trans(b, vbase + (dch >> 3) * SUB + v_tok * 128 + (((dch & 7) ^ lr) << 4));
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {  // 16-byte column 2jj + h
+          const uint32_t lo_t = b[2 * h], hi_t = b[2 * h + 1];  // tokens 0-7 / 8-15
+          const uint32_t be0 = fp8x2_to_h2<KV>(__byte_perm(lo_t, 0, 0x0020));
+          const uint32_t be1 = fp8x2_to_h2<KV>(__byte_perm(hi_t, 0, 0x0020));
+          const uint32_t bo0 = fp8x2_to_h2<KV>(__byte_perm(lo_t, 0, 0x0031));
+          const uint32_t bo1 = fp8x2_to_h2<KV>(__byte_perm(hi_t, 0, 0x0031));
+          mma_16816<false>(o[2 * (2 * jj + h)], pa, be0, be1);
+          mma_16816<false>(o[2 * (2 * jj + h) + 1], pa, bo0, bo1);
+        }
+      }
+    }
+
+    __syncwarp();
+    if (i + NSLOT < n_my) issue(i + NSLOT, slot);
+    if (++slot == NSLOT) {
+      slot = 0;
+      phase ^= 1;
+    }
+  }
+
+  // ---- merge the 4 warps through shared memory --------------------------------
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  __syncthreads();  // every issued TMA has been consumed: the rings are free
+  constexpr int OPAD = Cfg::OPAD;
+  float* sm_o = reinterpret_cast<float*>(smem);  // [kWarps][16][OPAD]
+  float* sm_m = sm_o + kWarps * 16 * OPAD;       // [kWarps][16]
+  float* sm_l = sm_m + kWarps * 16;
+  if (t == 0) {
+    sm_m[warp * 16 + g] = m0;
+    sm_m[warp * 16 + g + 8] = m1;
+    sm_l[warp * 16 + g] = l0;
+    sm_l[warp * 16 + g + 8] = l1;
+  }
+  {
+    float* r_lo = sm_o + (warp * 16 + g) * OPAD;
+    float* r_hi = sm_o + (warp * 16 + g + 8) * OPAD;
+#pragma unroll
+    for (int n = 0; n < 2 * KS; ++n) {
+      int d0, d1;
+      if constexpr (kFp8) {
+        d0 = 16 * (n >> 1) + 4 * t + (n & 1);
+        d1 = d0 + 2;
+      } else {
+        d0 = n * 8 + 2 * t;
+        d1 = d0 + 1;
+      }
+      r_lo[d0] = o[n][0];
+      r_lo[d1] = o[n][1];
+      if (rows > 8) {
+        r_hi[d0] = o[n][2];
+        r_hi[d1] = o[n][3];
+      }
+    }
+  }
+  __syncthreads();
+  const float vscale = (kFp8 && a.v_scale) ? *a.v_scale : 1.f;
+  for (int idx = threadIdx.x; idx < rows * D; idx += blockDim.x) {
+    const int row = idx / D, d = idx - row * D;
+    float mt = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) mt = fmaxf(mt, sm_m[w * 16 + row]);
+    float acc = 0.f, lt = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      const float mw = sm_m[w * 16 + row];
+      const float wgt = (mw == -INFINITY) ? 0.f : fast_exp2(mw - mt);
+      acc += sm_o[(w * 16 + row) * OPAD + d] * wgt;
+      lt += sm_l[w * 16 + row] * wgt;
+    }
+    const int qh = qh0 + row;
+    if (a.num_splits > 1) {
+      const int64_t pi = ((int64_t)seq * a.num_q_heads + qh) * a.num_splits + split;
+      a.part_o[pi * D + d] = acc;
+      if (d == 0) a.part_ml[pi] = make_float2(mt, lt);
+    } else {
+      QT* op = reinterpret_cast<QT*>(a.out) + (int64_t)seq * a.out_stride_seq + (int64_t)qh * a.out_stride_head;
+      op[d] = from_float<QT>(lt > 0.f ? acc / lt * vscale : 0.f);
+      if (d == 0 && a.out_lse)
+        a.out_lse[(int64_t)seq * a.num_q_heads + qh] = lt > 0.f ? (mt + log2f(lt)) * kLn2 : -INFINITY;
+    }
+  }
+}
+
+// ---- split combine:  m = max m_i;  o = sum o_i e^{m_i-m} / sum l_i e^{m_i-m} ------
+// (reduce_segments math, triton_unified_attention.py:735-759; partials hold
+// un-normalised accumulators like the Triton kernel, not the legacy v2 ones.)
+template <typename QT>
+__global__ void __launch_bounds__(128) paged_decode_combine_kernel(
+    QT* __restrict__ out, float* __restrict__ out_lse, const float* __restrict__ part_o,
+    const float2* __restrict__ part_ml, const float* __restrict__ v_scale, int num_q_heads, int num_splits, int D,
+    int64_t out_stride_seq, int64_t out_stride_head) {
+  const int h = blockIdx.x, seq = blockIdx.y;
+  const int64_t base = ((int64_t)seq * num_q_heads + h) * num_splits;
+  float mt = -INFINITY;
+  for (int i = 0; i < num_splits; ++i) mt = fmaxf(mt, part_ml[base + i].x);
+  float lt = 0.f;
+  for (int i = 0; i < num_splits; ++i) {
+    const float2 ml = part_ml[base + i];
+    lt += (ml.x == -INFINITY) ? 0.f : ml.y * fast_exp2(ml.x - mt);
+  }
+  const float vs = v_scale ? *v_scale : 1.f;
+  const float inv = lt > 0.f ? vs / lt : 0.f;
+  QT* op = out + (int64_t)seq * out_stride_seq + (int64_t)h * out_stride_head;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float acc = 0.f;
+    for (int i = 0; i < num_splits; ++i) {
+      const float mi = part_ml[base + i].x;
+      if (mi != -INFINITY) acc += part_o[(base + i) * D + d] * fast_exp2(mi - mt);
+    }
+    op[d] = from_float<QT>(acc * inv);
+  }
+  if (threadIdx.x == 0 && out_lse)
+    out_lse[(int64_t)seq * num_q_heads + h] = lt > 0.f ? (mt + log2f(lt)) * kLn2 : -INFINITY;
+}
+
+// ---- host side ------------------------------------------------------------------
+struct TmapKey {
+  const void* base;
+  int64_t s0, s1, s2, nb;
+  int d, h, bs, es;
+  bool operator==(const TmapKey& o) const {
+    return base == o.base && s0 == o.s0 && s1 == o.s1 && s2 == o.s2 && nb == o.nb && d == o.d && h == o.h &&
+           bs == o.bs && es == o.es;
+  }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    size_t x = reinterpret_cast<size_t>(k.base);
+    auto mix = [&](uint64_t v) { x ^= v + 0x9e3779b97f4a7c15ull + (x << 6) + (x >> 2); };
+    mix(k.s0); mix(k.s1); mix(k.s2); mix(k.nb); mix(k.d); mix(k.h); mix(k.bs); mix(k.es);
+    return x;
+  }
+};
+
+// [D, H, block_size, num_blocks] view of a paged cache, box = one 128-byte span x 16 tokens.
+static int get_cache_tmap(CUtensorMap* out, const void* base, int D, int H, int block_size, int64_t num_blocks,
+                          int64_t head_stride, int64_t page_stride, int64_t block_stride, int es) {
+  static std::mutex mu;
+  static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> cache;
+  TmapKey key{base, head_stride, page_stride, block_stride, num_blocks, D, H, block_size, es};
+  std::lock_guard<std::mutex> lk(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) {
+    *out = it->second;
+    return 0;
+  }
+  uint64_t dims[4] = {(uint64_t)D, (uint64_t)H, (uint64_t)block_size, (uint64_t)num_blocks};
+  uint64_t strides[3] = {(uint64_t)head_stride * es, (uint64_t)page_stride * es, (uint64_t)block_stride * es};
+  uint32_t box[4] = {(uint32_t)(128 / es), 1, (uint32_t)kChunk, 1};
+  CUtensorMap tm;
+  int rc = encode_tmap(&tm, es == 2 ? kTmaU16 : kTmaU8, 4, base, dims, strides, box, kSwizzle128);
+  if (rc) return rc;
+  if (cache.size() > 4096) cache.clear();
+  cache.emplace(key, tm);
+  *out = tm;
+  return 0;
+}
+
+template <typename QT, int D, int KV>
+static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeArgs& a, int num_seqs,
+                         cudaStream_t stream) {
+  using Cfg = DecodeCfg<D, KV>;
+  static bool attr_set = false;
+  auto kern = paged_decode_kernel<QT, D, KV>;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
+      return B200_ERR_CUDA;
+    }
+    attr_set = true;
+  }
+  dim3 grid(a.num_splits, a.num_kv_heads * a.qgroups, num_seqs);
+  kern<<<grid, kWarps * 32, Cfg::SMEM_BYTES, stream>>>(tk, tv, a);
+  B200_CHECK_LAUNCH();
+  count_launch();
+  if (a.num_splits > 1) {
+    dim3 g2(a.num_q_heads, num_seqs);
+    paged_decode_combine_kernel<QT><<<g2, 128, 0, stream>>>(
+        reinterpret_cast<QT*>(a.out), a.out_lse, a.part_o, a.part_ml, KV == B200_KV_AUTO ? nullptr : a.v_scale,
+        a.num_q_heads, a.num_splits, D, a.out_stride_seq, a.out_stride_head);
+    B200_CHECK_LAUNCH();
+    count_launch();
+  }
+  return 0;
+}
+
+}  // namespace b200
+
+extern "C" size_t b200_paged_decode_workspace_bytes(int num_seqs, int num_q_heads, int head_size, int num_splits) {
+  if (num_splits <= 1) return 0;
+  return (size_t)num_seqs * num_q_heads * num_splits * ((size_t)head_size * 4 + 8);
+}
+
+extern "C" int b200_paged_decode_pick_splits(int num_seqs, int num_kv_heads, int max_seq_len, int sm_count) {
+  // Deterministic in its arguments only (CUDA-graph safe).  Aim for ~8 waves of
+  // 2 resident CTAs per SM so the tail is <~10% while every split still streams
+  // at least 16 chunks (256 tokens) to amortise its prologue/merge.
+  if (sm_count <= 0) sm_count = 148;
+  const long base = (long)num_seqs * num_kv_heads;
+  if (base <= 0) return 1;
+  const int chunks = (max_seq_len + b200::kChunk - 1) / b200::kChunk;
+  long want = (8L * 2 * sm_count + base - 1) / base;
+  long cap = chunks / 16;
+  if (cap < 1) cap = 1;
+  long s = want < cap ? want : cap;
+  if (s > 128) s = 128;
+  if (s < 1) s = 1;
+  return (int)s;
+}
+
+extern "C" int b200_paged_attention_decode(const b200_paged_decode_params* p, b200_stream_t stream) {
+  using namespace b200;
+  B200_CHECK_ARG(p != nullptr, B200_ERR_INVALID_ARG, "paged_attention_decode: null params");
+  B200_CHECK_ARG(p->num_seqs >= 0 && p->num_q_heads > 0 && p->num_kv_heads > 0 && p->head_size > 0 &&
+                     p->block_size > 0,
+                 B200_ERR_INVALID_ARG, "paged_attention_decode: bad sizes");
+  B200_CHECK_ARG(p->num_q_heads % p->num_kv_heads == 0, B200_ERR_INVALID_ARG,
+                 "paged_attention_decode: num_q_heads (%d) must be a multiple of num_kv_heads (%d)", p->num_q_heads,
+                 p->num_kv_heads);
+  B200_CHECK_ARG(p->block_size % kChunk == 0, B200_ERR_UNSUPPORTED,
+                 "paged_attention_decode: block_size %d must be a multiple of 16", p->block_size);
+  B200_CHECK_ARG(p->q_dtype == B200_DT_BF16 || p->q_dtype == B200_DT_F16, B200_ERR_UNSUPPORTED,
+                 "paged_attention_decode: query dtype must be fp16 or bf16");
+  B200_CHECK_ARG(p->kv_dtype == B200_KV_AUTO || p->kv_dtype == B200_KV_FP8_E4M3 || p->kv_dtype == B200_KV_FP8_E5M2,
+                 B200_ERR_INVALID_ARG, "paged_attention_decode: Unsupported data type of kv cache: %d", p->kv_dtype);
+  if (p->num_seqs == 0) return 0;
+  B200_CHECK_ARG(p->out && p->query && p->key_cache && p->value_cache && p->block_table && p->seq_lens,
+                 B200_ERR_INVALID_ARG, "paged_attention_decode: null pointer");
+  const int es = p->kv_dtype == B200_KV_AUTO ? 2 : 1;
+  const int D = p->head_size;
+  B200_CHECK_ARG((D == 64 && es == 2) || D == 128 || D == 256, B200_ERR_UNSUPPORTED,
+                 "paged_attention_decode: head_size %d with %d-byte cache elements is not built "
+                 "(supported: 64 (16-bit), 128, 256)",
+                 D, es);
+  B200_CHECK_ARG((p->q_stride_seq % 2 == 0) && (p->q_stride_head % 2 == 0) &&
+                     (reinterpret_cast<uintptr_t>(p->query) % 4 == 0),
+                 B200_ERR_ALIGNMENT, "paged_attention_decode: query must be 4-byte aligned with even strides");
+  auto tma_ok = [&](const void* base, int64_t hs, int64_t ps, int64_t bs) {
+    return reinterpret_cast<uintptr_t>(base) % 16 == 0 && (hs * es) % 16 == 0 && (ps * es) % 16 == 0 &&
+           (bs * es) % 16 == 0;
+  };
+  B200_CHECK_ARG(tma_ok(p->key_cache, p->kv_head_stride, p->kv_page_stride, p->kv_block_stride) &&
+                     tma_ok(p->value_cache, p->v_head_stride, p->v_page_stride, p->v_block_stride),
+                 B200_ERR_ALIGNMENT, "paged_attention_decode: cache base and strides must be 16-byte multiples");
+  B200_CHECK_ARG(p->num_blocks > 0, B200_ERR_INVALID_ARG, "paged_attention_decode: num_blocks must be > 0");
+
+  DecodeArgs a;
+  a.out = p->out;
+  a.query = p->query;
+  a.block_table = p->block_table;
+  a.seq_lens = p->seq_lens;
+  a.k_scale = p->k_scale;
+  a.v_scale = p->v_scale;
+  a.out_lse = p->out_lse;
+  a.q_stride_seq = p->q_stride_seq;
+  a.q_stride_head = p->q_stride_head;
+  a.out_stride_seq = p->out_stride_seq;
+  a.out_stride_head = p->out_stride_head;
+  a.block_table_stride = p->block_table_stride;
+  a.num_q_heads = p->num_q_heads;
+  a.num_kv_heads = p->num_kv_heads;
+  a.group = p->num_q_heads / p->num_kv_heads;
+  a.qgroups = (a.group + 15) / 16;
+  a.block_size = p->block_size;
+  a.sliding_window = p->sliding_window > 0 ? p->sliding_window : 0;
+  a.scale = p->scale;
+  a.soft_cap = p->logits_soft_cap;
+  int splits = p->num_splits;
+  if (splits <= 0)
+    splits = b200_paged_decode_pick_splits(p->num_seqs, p->num_kv_heads * a.qgroups,
+                                           p->max_seq_len > 0 ? p->max_seq_len : 1, sm_count());
+  a.num_splits = splits;
+  a.part_o = nullptr;
+  a.part_ml = nullptr;
+  if (splits > 1) {
+    const size_t need = b200_paged_decode_workspace_bytes(p->num_seqs, p->num_q_heads, D, splits);
+    B200_CHECK_ARG(p->workspace && p->workspace_bytes >= need, B200_ERR_WORKSPACE,
+                   "paged_attention_decode: workspace %zu bytes < required %zu (splits=%d)", p->workspace_bytes,
+                   need, splits);
+    B200_CHECK_ARG(reinterpret_cast<uintptr_t>(p->workspace) % 16 == 0, B200_ERR_ALIGNMENT,
+                   "paged_attention_decode: workspace must be 16-byte aligned");
+    a.part_o = reinterpret_cast<float*>(p->workspace);
+    a.part_ml = reinterpret_cast<float2*>(a.part_o + (size_t)p->num_seqs * p->num_q_heads * splits * D);
+  }
+  CUtensorMap tk, tv;
+  int rc = get_cache_tmap(&tk, p->key_cache, D, p->num_kv_heads, p->block_size, p->num_blocks, p->kv_head_stride,
+                          p->kv_page_stride, p->kv_block_stride, es);
+  if (rc) return rc;
+  rc = get_cache_tmap(&tv, p->value_cache, D, p->num_kv_heads, p->block_size, p->num_blocks, p->v_head_stride,
+                      p->v_page_stride, p->v_block_stride, es);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+#define B200_DISPATCH_D(QT, KV)                                                    \
+  switch (D) {                                                                     \
+    case 128: return launch_decode<QT, 128, KV>(tk, tv, a, p->num_seqs, s);        \
+    case 256: return launch_decode<QT, 256, KV>(tk, tv, a, p->num_seqs, s);        \
+    default: break;                                                                \
+  }
+  if (p->kv_dtype == B200_KV_AUTO) {
+    if (p->q_dtype == B200_DT_BF16) {
+      if (D == 64) return launch_decode<__nv_bfloat16, 64, B200_KV_AUTO>(tk, tv, a, p->num_seqs, s);
+      B200_DISPATCH_D(__nv_bfloat16, B200_KV_AUTO)
+    } else {
+      if (D == 64) return launch_decode<__half, 64, B200_KV_AUTO>(tk, tv, a, p->num_seqs, s);
+      B200_DISPATCH_D(__half, B200_KV_AUTO)
+    }
+  } else if (p->kv_dtype == B200_KV_FP8_E4M3) {
+    if (p->q_dtype == B200_DT_BF16) {
+      B200_DISPATCH_D(__nv_bfloat16, B200_KV_FP8_E4M3)
+    } else {
+      B200_DISPATCH_D(__half, B200_KV_FP8_E4M3)
+    }
+  } else {
+    if (p->q_dtype == B200_DT_BF16) {
+      B200_DISPATCH_D(__nv_bfloat16, B200_KV_FP8_E5M2)
+    } else {
+      B200_DISPATCH_D(__half, B200_KV_FP8_E5M2)
+    }
+  }
+#undef B200_DISPATCH_D
+  set_error("paged_attention_decode: no kernel for head_size %d", D);
+  return B200_ERR_UNSUPPORTED;
+}

@@ -1,0 +1,229 @@
+"""Minimal tensor-parallel decode-step runner over the C-ABI kernels.
+
+This is NOT vLLM's model runner (that stays vLLM's — see INTEGRATION.md); it is the
+smallest harness that executes exactly the decode step of SURVEY §3.1 for a Llama-style
+dense model so bench.py / smoke() / tests can time and check the hot path end to end:
+
+  per layer:  fused-add RMSNorm -> FP8 per-token quant -> qkv GEMM -> RoPE ->
+              KV-cache write (slot_mapping) -> paged-attention decode (block_table) ->
+              quant -> o_proj GEMM -> [all-reduce] -> fused-add RMSNorm -> quant ->
+              gate_up GEMM -> SiLU*mul -> quant -> down GEMM -> [all-reduce]
+  then:       final norm -> lm_head (vocab-parallel library GEMM) -> greedy argmax.
+
+Tensor parallelism follows vLLM's sharding (vllm/model_executor/layers/linear.py: QKV /
+gate_up column-parallel by head / column, o_proj / down_proj row-parallel + all-reduce at
+linear.py:1657-1660): one process per GPU, `torch.distributed` NCCL all-reduce, every rank
+owns the KV cache of its own kv-heads with the same block_table / slot_mapping.
+Weights are synthetic ("dummy" load format) and quantised online per tensor like
+Fp8PerTensorOnlineLinearMethod (vllm/model_executor/layers/quantization/online/fp8.py:158-224).
+"""
+from __future__ import annotations
+
+import dataclasses
+import math
+
+import torch
+import torch.distributed as dist
+
+from . import _lib, ops
+
+
+@dataclasses.dataclass
+class ModelShape:
+    name: str = "llama-3.1-8b"
+    num_layers: int = 32
+    hidden: int = 4096
+    num_q_heads: int = 32
+    num_kv_heads: int = 8
+    head_size: int = 128
+    intermediate: int = 14336
+    vocab: int = 128256
+    rope_theta: float = 500000.0
+    rms_eps: float = 1e-5
+
+
+LLAMA_8B = ModelShape()
+LLAMA_70B = ModelShape("llama-3.1-70b", 80, 8192, 64, 8, 128, 28672, 128256)
+OPT_125M_LIKE = ModelShape("opt-125m-shape", 12, 768, 12, 12, 64, 3072, 50272, 10000.0)
+
+
+class DecodeRunner:
+    """Owns per-rank weights + paged KV caches and runs one decode step (optionally as a CUDA graph)."""
+
+    def __init__(self, shape: ModelShape, batch: int, max_ctx: int, *, block_size: int = 16,
+                 kv_cache_dtype: str = "fp8", weight_quant: str = "fp8", tp_size: int = 1, tp_rank: int = 0,
+                 device: torch.device | str = "cuda:0", seed: int = 0, num_layers: int | None = None,
+                 tp_group=None):
+        self.s = shape
+        self.B, self.max_ctx, self.bs = batch, max_ctx, block_size
+        self.kv_dtype, self.wq = kv_cache_dtype, weight_quant
+        self.tp, self.rank, self.group = tp_size, tp_rank, tp_group
+        self.dev = torch.device(device)
+        self.L = num_layers if num_layers is not None else shape.num_layers
+        assert shape.num_q_heads % tp_size == 0 and shape.num_kv_heads % tp_size == 0
+        assert shape.intermediate % tp_size == 0 and weight_quant in ("fp8", "nvfp4")
+        self.Hq, self.Hkv, self.D = shape.num_q_heads // tp_size, shape.num_kv_heads // tp_size, shape.head_size
+        self.inter = shape.intermediate // tp_size
+        self.vocab_shard = (shape.vocab + tp_size - 1) // tp_size
+        self.dtype = torch.bfloat16
+        g = torch.Generator(device=self.dev)
+        g.manual_seed(seed * 1000 + tp_rank)
+        gshared = torch.Generator(device=self.dev)
+        gshared.manual_seed(seed)  # tensors that must be identical on every rank
+        H = shape.hidden
+
+        def w(n, k):
+            return (torch.randn(n, k, device=self.dev, generator=g, dtype=torch.float32) * 0.02).to(self.dtype)
+
+        self.layers = []
+        for _ in range(self.L):
+            lw = {
+                "qkv": self._quant_weight(w((self.Hq + 2 * self.Hkv) * self.D, H)),
+                "o": self._quant_weight(w(H, self.Hq * self.D)),
+                "gate_up": self._quant_weight(w(2 * self.inter, H)),
+                "down": self._quant_weight(w(H, self.inter)),
+                "ln1": torch.ones(H, device=self.dev, dtype=self.dtype),
+                "ln2": torch.ones(H, device=self.dev, dtype=self.dtype),
+            }
+            self.layers.append(lw)
+        self.final_ln = torch.ones(H, device=self.dev, dtype=self.dtype)
+        self.embed = (torch.randn(shape.vocab, H, device=self.dev, generator=gshared, dtype=torch.float32) * 0.02).to(self.dtype)
+        self.lm_head = w(self.vocab_shard, H)
+        # rotary cache [max_pos, rot_dim] = cos | sin
+        inv = 1.0 / (shape.rope_theta ** (torch.arange(0, self.D, 2, device=self.dev).float() / self.D))
+        fr = torch.outer(torch.arange(max_ctx + 8, device=self.dev).float(), inv)
+        self.cos_sin = torch.cat([fr.cos(), fr.sin()], -1).to(self.dtype)
+        # paged KV cache, vLLM 0.22 layout (2, num_blocks, block_size, Hkv, D) per layer
+        self.blocks_per_seq = (max_ctx + block_size - 1) // block_size
+        self.num_blocks = batch * self.blocks_per_seq + 1
+        cdt = torch.uint8 if kv_cache_dtype.startswith("fp8") else self.dtype
+        self.kv_caches = []
+        for _ in range(self.L):
+            kv = torch.empty(2, self.num_blocks, block_size, self.Hkv, self.D, device=self.dev, dtype=cdt)
+            if cdt == torch.uint8:  # random finite e4m3 bytes (exponent field != 0xF)
+                kv.copy_(torch.randint(0, 256, kv.shape, device=self.dev, generator=g, dtype=torch.uint8) & 0x77)
+            else:
+                kv.copy_(((torch.rand(kv.shape, device=self.dev, generator=g) * 2 - 1) * self.D ** -0.5).to(cdt))
+            self.kv_caches.append(kv)
+        self.k_scale = torch.tensor([0.05], device=self.dev)
+        self.v_scale = torch.tensor([0.05], device=self.dev)
+        # static step buffers (CUDA-graph inputs)
+        self.input_ids = torch.zeros(batch, dtype=torch.int64, device=self.dev)
+        self.positions = torch.zeros(batch, dtype=torch.int64, device=self.dev)
+        self.slot_mapping = torch.zeros(batch, dtype=torch.int64, device=self.dev)
+        self.seq_lens = torch.zeros(batch, dtype=torch.int32, device=self.dev)
+        self.block_table = torch.zeros(batch, self.blocks_per_seq, dtype=torch.int32, device=self.dev)
+        self.query_start_loc = torch.arange(batch + 1, dtype=torch.int32, device=self.dev)
+        self.next_tokens = torch.zeros(batch, dtype=torch.int64, device=self.dev)
+        self.num_splits = ops.paged_decode_num_splits(batch, self.Hq, self.Hkv, max_ctx, self.dev)
+        ws = ops.paged_decode_workspace_bytes(batch, self.Hq, self.D, self.num_splits)
+        self.attn_ws = torch.empty(max(ws, 16), dtype=torch.uint8, device=self.dev)
+        self.scale = self.D ** -0.5
+        self.graph: torch.cuda.CUDAGraph | None = None
+        self.launches_per_step = 0
+
+    # ----------------------------------------------------------------- weights / linears
+    def _quant_weight(self, w: torch.Tensor):
+        if self.wq == "fp8":
+            q, s = ops.scaled_fp8_quant(w)  # per tensor, [N,K] K-contiguous == column-major [K,N]
+            return {"w": q, "s": s}
+        gs = (448.0 * 6.0 / w.abs().max().float()).reshape(1)
+        q, sf = ops.scaled_fp4_quant(w, gs)
+        return {"w": q, "sf": sf, "gs": gs}
+
+    def _linear(self, x: torch.Tensor, lw) -> torch.Tensor:
+        if self.wq == "fp8":
+            xq, xs = ops.scaled_fp8_quant(x, use_per_token_if_dynamic=True)
+            return ops.cutlass_scaled_mm(xq, lw["w"].t(), xs, lw["s"], self.dtype)
+        # NVFP4: static activation global scale (ModelOpt input_scale), here a fixed calibration constant
+        if "ags" not in lw:
+            lw["ags"] = torch.tensor([448.0 * 6.0 / 8.0], device=self.dev)
+            lw["alpha"] = (1.0 / (lw["ags"] * lw["gs"])).float()
+        xq, xsf = ops.scaled_fp4_quant(x, lw["ags"])
+        return ops.cutlass_scaled_fp4_mm(xq, lw["w"], xsf, lw["sf"], lw["alpha"], self.dtype)
+
+    def _all_reduce(self, x: torch.Tensor) -> torch.Tensor:
+        if self.tp > 1:
+            dist.all_reduce(x, group=self.group)
+        return x
+
+    # ----------------------------------------------------------------------- the step
+    def set_batch(self, seq_len: int, block_table: torch.Tensor | None = None, seed: int = 0) -> None:
+        """Synthetic decode state: every sequence has `seq_len` tokens, the newest at position seq_len-1."""
+        g = torch.Generator(device=self.dev)
+        g.manual_seed(1234 + seed)  # same on every rank: the scheduler state is global
+        if block_table is None:
+            perm = torch.randperm(self.num_blocks - 1, device=self.dev, generator=g)[: self.B * self.blocks_per_seq] + 1
+            block_table = perm.reshape(self.B, self.blocks_per_seq).to(torch.int32)
+        self.block_table.copy_(block_table)
+        self.seq_lens.fill_(seq_len)
+        self.positions.fill_(seq_len - 1)
+        self.input_ids.copy_(torch.randint(0, self.s.vocab, (self.B,), device=self.dev, generator=g))
+        ops.compute_slot_mapping(self.query_start_loc, self.positions, self.block_table, self.bs, self.slot_mapping)
+
+    def step_eager(self) -> torch.Tensor:
+        s, B = self.s, self.B
+        hidden = self.embed[self.input_ids]
+        residual = torch.zeros_like(hidden)
+        attn_out = torch.empty(B, self.Hq, self.D, device=self.dev, dtype=self.dtype)
+        for lw, kv in zip(self.layers, self.kv_caches):
+            ops.fused_add_rms_norm(hidden, residual, lw["ln1"], s.rms_eps)
+            qkv = self._linear(hidden, lw["qkv"])
+            q, k, v = qkv.split([self.Hq * self.D, self.Hkv * self.D, self.Hkv * self.D], dim=-1)
+            ops.rotary_embedding(self.positions, q, k, self.D, self.cos_sin)
+            kc, vc = kv.unbind(0)
+            ops.reshape_and_cache_flash(k.view(B, self.Hkv, self.D), v.view(B, self.Hkv, self.D), kc, vc,
+                                        self.slot_mapping, self.kv_dtype, self.k_scale, self.v_scale)
+            ops.paged_attention_decode(attn_out, q.view(B, self.Hq, self.D), kc, vc, self.block_table, self.seq_lens,
+                                       self.scale, self.max_ctx, self.kv_dtype, self.k_scale, self.v_scale,
+                                       num_splits=self.num_splits, workspace=self.attn_ws)
+            hidden = self._all_reduce(self._linear(attn_out.view(B, -1), lw["o"]))
+            ops.fused_add_rms_norm(hidden, residual, lw["ln2"], s.rms_eps)
+            gu = self._linear(hidden, lw["gate_up"])
+            act = torch.empty(B, self.inter, device=self.dev, dtype=self.dtype)
+            ops.silu_and_mul(act, gu)
+            hidden = self._all_reduce(self._linear(act, lw["down"]))
+        ops.fused_add_rms_norm(hidden, residual, self.final_ln, s.rms_eps)
+        logits = torch.matmul(hidden, self.lm_head.t())  # plain library GEMM (bf16 lm_head, as in vLLM)
+        if self.tp == 1:
+            self.next_tokens.copy_(logits.argmax(-1))
+        else:
+            mx, idx = logits.float().max(-1)
+            both = torch.stack([mx, (idx + self.rank * self.vocab_shard).float()], -1)
+            gathered = [torch.empty_like(both) for _ in range(self.tp)]
+            dist.all_gather(gathered, both, group=self.group)
+            allv = torch.stack(gathered, 0)
+            win = allv[..., 0].argmax(0)
+            self.next_tokens.copy_(allv[win, torch.arange(B, device=self.dev), 1].long())
+        return self.next_tokens
+
+    def capture(self, warmup: int = 2) -> None:
+        """Capture the step into a CUDA graph (what vLLM's FULL cudagraph mode does for decode)."""
+        side = torch.cuda.Stream(self.dev)
+        side.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self.step_eager()
+        torch.cuda.current_stream(self.dev).wait_stream(side)
+        torch.cuda.synchronize(self.dev)
+        before = _lib.num_kernels_launched()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.step_eager()
+        self.launches_per_step = _lib.num_kernels_launched() - before
+
+    def step(self) -> torch.Tensor:
+        if self.graph is not None:
+            self.graph.replay()
+            return self.next_tokens
+        return self.step_eager()
+
+    # --------------------------------------------------------------------- accounting
+    def attention_bytes_per_layer(self, seq_len: int) -> int:
+        """sum_s len_s * Hkv * D * 2 * kv_itemsize + B * Hq * D * (2 + 2)."""
+        it = 1 if self.kv_dtype.startswith("fp8") else 2
+        return self.B * seq_len * self.Hkv * self.D * 2 * it + self.B * self.Hq * self.D * 4
+
+    def weight_bytes_per_layer(self) -> int:
+        n = sum(lw["w"].numel() * lw["w"].element_size() for lw in self.layers[0].values() if isinstance(lw, dict))
+        return n

@@ -312,10 +312,11 @@ _mm_workspaces: dict[tuple[int, int], torch.Tensor] = {}
 
 
 def _mm_workspace(device: torch.device, nbytes: int) -> torch.Tensor | None:
-    """Zero-initialised split-K scratch, one per (device, stream); kernels leave it zeroed."""
+    """Zero-initialised split-K scratch, one per device (GEMMs of one process are issued on one
+    stream at a time, like vLLM's worker); kernels leave it zeroed."""
     if nbytes <= 0:
         return None
-    key = (device.index or 0, torch.cuda.current_stream(device).cuda_stream)
+    key = (device.index or 0, 0)
     ws = _mm_workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         if torch.cuda.is_current_stream_capturing():

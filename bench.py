@@ -173,6 +173,17 @@ def run_ours(args) -> None:
     runner = DecodeRunner(LLAMA_8B, B, ctx, kv_cache_dtype="fp8", weight_quant="fp8", tp_size=world, tp_rank=rank,
                           device=dev, tp_group=group, num_layers=args.layers)
     runner.set_batch(ctx)
+    if args.profile_step:
+        # for `ncu --profile-from-start off`: exactly one eager step between profiler start/stop
+        runner.step_eager()
+        runner.step_eager()
+        torch.cuda.synchronize(dev)
+        torch.cuda.profiler.start()
+        runner.step_eager()
+        torch.cuda.synchronize(dev)
+        torch.cuda.profiler.stop()
+        print(json.dumps({"profile_step": True, "launches_ours": _lib.num_kernels_launched()}))
+        return
     runner.capture(warmup=2)
 
     def barrier():
@@ -304,6 +315,7 @@ def main() -> None:
     ap.add_argument("--ctx", type=int, default=4096)
     ap.add_argument("--layers", type=int, default=None, help="debug only: fewer layers (INVALID as a bench number)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-step", action="store_true", help="run one eager step between cudaProfilerStart/Stop")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -120,6 +120,11 @@ typedef struct b200_paged_decode_params {
   const float* k_scale;       /* device scalar or NULL (=1)                  */
   const float* v_scale;
   float* out_lse;             /* optional                                    */
+  const int32_t* token_to_seq; /* optional [num_seqs]: block_table row of each
+                                 query token (NULL = identity).  Lets a chunked-
+                                 prefill / mixed batch run as one single-query
+                                 attention per token with its own causal length
+                                 in seq_lens[token].                          */
   void* workspace;
   size_t workspace_bytes;
   int64_t q_stride_seq, q_stride_head;     /* elements                      */

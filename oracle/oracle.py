@@ -34,6 +34,15 @@ def to_fp8(x: torch.Tensor, kind: str = "e4m3") -> torch.Tensor:
     return torch.clamp(x.float(), -FP8_E5M2_MAX, FP8_E5M2_MAX).to(torch.float8_e5m2)
 
 
+def clamp_to_e4m3(x: torch.Tensor) -> torch.Tensor:
+    """scaled_fp8_conversion (csrc/quantization/w8a8/fp8/common.cuh:57-76):
+    r = fmaxf(-448, fminf(x, 448)) then the hardware cvt.  fminf/fmaxf drop a NaN operand,
+    so NaN (0 * inf when a whole tensor is zero) becomes +448 — unlike torch.clamp."""
+    hi = torch.tensor(FP8_E4M3_MAX, dtype=torch.float32)
+    r = torch.fmax(-hi, torch.fmin(x.float(), hi))
+    return r.to(torch.float8_e4m3fn)
+
+
 def fp8_kind(kv_cache_dtype: str) -> str | None:
     """csrc/attention/dtype_fp8.cuh:21 get_fp8_kv_cache_data_type."""
     if kv_cache_dtype in ("auto", "bfloat16", "float16", "half"):
@@ -163,7 +172,7 @@ def merge_attn_states(prefix_output, prefix_lse, suffix_output, suffix_lse):
 def static_scaled_fp8_quant(x, scale):
     """fp8/common.cu:13-76 + common.cuh:57-76: e4m3(clamp(x * (1/scale)))."""
     inv = (torch.ones((), dtype=torch.float32) / scale.float())
-    return to_fp8(x.float() * inv)
+    return clamp_to_e4m3(x.float() * inv)
 
 
 def dynamic_scaled_fp8_quant(x):
@@ -180,7 +189,7 @@ def dynamic_per_token_scaled_fp8_quant(x, scale_ub=None):
     fmax = torch.tensor(FP8_E4M3_MAX, dtype=torch.float32)
     min_s = torch.tensor(1.0, dtype=torch.float32) / (fmax * torch.tensor(512.0, dtype=torch.float32))
     s = torch.maximum(amax / fmax, min_s)
-    return to_fp8(x.float() / s), s
+    return clamp_to_e4m3(x.float() / s), s
 
 
 def scaled_mm(a_fp8, b_fp8, scale_a, scale_b, out_dtype, bias=None):

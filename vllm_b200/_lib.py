@@ -26,7 +26,7 @@ class PagedDecodeParams(C.Structure):
     _fields_ = [
         ("out", vp), ("query", vp), ("key_cache", vp), ("value_cache", vp),
         ("block_table", vp), ("seq_lens", vp), ("k_scale", vp), ("v_scale", vp),
-        ("out_lse", vp), ("workspace", vp), ("workspace_bytes", sz),
+        ("out_lse", vp), ("token_to_seq", vp), ("workspace", vp), ("workspace_bytes", sz),
         ("q_stride_seq", i64), ("q_stride_head", i64),
         ("out_stride_seq", i64), ("out_stride_head", i64),
         ("kv_block_stride", i64), ("kv_page_stride", i64), ("kv_head_stride", i64),

@@ -59,6 +59,7 @@ struct DecodeArgs {
   const float* k_scale;
   const float* v_scale;
   float* out_lse;
+  const int32_t* token_to_seq;  // optional: block_table row per query token
   float* part_o;   // [seq][hq][split][D]
   float2* part_ml; // [seq][hq][split]
   int64_t q_stride_seq, q_stride_head, out_stride_seq, out_stride_head, block_table_stride;
@@ -203,7 +204,8 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
   const int n_my = span > warp ? (span - warp + kWarps - 1) / kWarps : 0;
   uint8_t* ring = smem + warp * NSLOT * Cfg::SLOT_BYTES;
   uint64_t* wbar = bars + warp * NSLOT;
-  const int32_t* bt_row = a.block_table + (int64_t)seq * a.block_table_stride;
+  const int32_t* bt_row =
+      a.block_table + (int64_t)(a.token_to_seq ? a.token_to_seq[seq] : seq) * a.block_table_stride;
   auto load_ids = [&](int batch) -> int {
     const int i = batch * 32 + lane;
     if (i < n_my) return bt_row[((c0 + warp + kWarps * i) * kChunk) / a.block_size];
@@ -625,6 +627,7 @@ extern "C" int b200_paged_attention_decode(const b200_paged_decode_params* p, b2
   a.k_scale = p->k_scale;
   a.v_scale = p->v_scale;
   a.out_lse = p->out_lse;
+  a.token_to_seq = p->token_to_seq;
   a.q_stride_seq = p->q_stride_seq;
   a.q_stride_head = p->q_stride_head;
   a.out_stride_seq = p->out_stride_seq;

@@ -157,8 +157,10 @@ def paged_attention_decode(
     out_lse: torch.Tensor | None = None,
     logits_soft_cap: float = 0.0,
     sliding_window: int = 0,
+    token_to_seq: torch.Tensor | None = None,
 ) -> torch.Tensor:
-    """One query token per sequence.  query/out [S, Hq, D]; caches are 4-D views
+    """One query token per sequence (or, with token_to_seq int32 [S], one per query token of a
+    mixed batch: row s reads block_table[token_to_seq[s]] with causal length seq_lens[s]).  query/out [S, Hq, D]; caches are 4-D views
     (num_blocks, block_size, Hkv, D) with any strides; block_table int32 [S, max_blocks];
     seq_lens int32 [S].  fp8 caches are uint8 / float8 storage + per-tensor k/v scales."""
     _require_cuda(out, query, key_cache, value_cache, block_table, seq_lens)
@@ -185,7 +187,7 @@ def paged_attention_decode(
     p = _lib.PagedDecodeParams(
         out=out.data_ptr(), query=query.data_ptr(), key_cache=key_cache.data_ptr(),
         value_cache=value_cache.data_ptr(), block_table=block_table.data_ptr(), seq_lens=seq_lens.data_ptr(),
-        k_scale=_ptr(k_scale), v_scale=_ptr(v_scale), out_lse=_ptr(out_lse),
+        k_scale=_ptr(k_scale), v_scale=_ptr(v_scale), out_lse=_ptr(out_lse), token_to_seq=_ptr(token_to_seq),
         workspace=_ptr(workspace), workspace_bytes=0 if workspace is None else workspace.numel() * workspace.element_size(),
         q_stride_seq=query.stride(0), q_stride_head=query.stride(1),
         out_stride_seq=out.stride(0), out_stride_head=out.stride(1),

@@ -239,9 +239,11 @@ def scaled_fp8_quant(
     use_per_token_if_dynamic: bool = False,
     output: torch.Tensor | None = None,
     group_shape: tuple[int, int] | None = None,
+    scale_out: torch.Tensor | None = None,
 ) -> tuple[torch.Tensor, torch.Tensor]:
     """Same contract as vllm/_custom_ops.py:1832-1899: scale given -> static; else
-    dynamic per-tensor, or dynamic per-token when use_per_token_if_dynamic."""
+    dynamic per-tensor, or dynamic per-token when use_per_token_if_dynamic.  `scale_out`
+    (ours) lets the torch.ops `Tensor! scale` variants write a caller-allocated scale."""
     _require_cuda(input, scale, scale_ub, output)
     if input.dim() != 2:
         raise RuntimeError("scaled_fp8_quant: input must be 2-D")
@@ -256,13 +258,17 @@ def scaled_fp8_quant(
     lib, st, dt = _lib.load(), _stream(input), _dt(input)
     if scale is None:
         if use_per_token_if_dynamic:
-            scale = torch.empty((M, 1), device=input.device, dtype=torch.float32)
+            scale = scale_out if scale_out is not None else torch.empty((M, 1), device=input.device, dtype=torch.float32)
+            if scale.numel() != M or scale.dtype != torch.float32 or not scale.is_contiguous():
+                raise RuntimeError("dynamic_per_token_scaled_fp8_quant: scale must be contiguous float32 with one entry per token")
             rc = lib.b200_dynamic_per_token_scaled_fp8_quant(
                 output.data_ptr(), input.data_ptr(), scale.data_ptr(), _ptr(scale_ub), M, K, input.stride(0),
                 output.stride(0), dt, st)
             _lib.check(rc, "dynamic_per_token_scaled_fp8_quant")
         else:
-            scale = torch.empty(1, device=input.device, dtype=torch.float32)
+            scale = scale_out if scale_out is not None else torch.empty(1, device=input.device, dtype=torch.float32)
+            if scale.numel() != 1 or scale.dtype != torch.float32:
+                raise RuntimeError("dynamic_scaled_fp8_quant: scale must be a float32 tensor with one element")
             rc = lib.b200_dynamic_scaled_fp8_quant(output.data_ptr(), input.data_ptr(), scale.data_ptr(), M, K,
                                                    input.stride(0), output.stride(0), dt, st)
             _lib.check(rc, "dynamic_scaled_fp8_quant")
@@ -335,6 +341,7 @@ def cutlass_scaled_mm(
     scale_b: torch.Tensor,
     out_dtype: torch.dtype,
     bias: torch.Tensor | None = None,
+    out: torch.Tensor | None = None,
 ) -> torch.Tensor:
     """out = (scale_a * a) @ (scale_b * b) + bias; a [M,K] row-major e4m3, b [K,N]
     column-major (b.stride(0) == 1), scales fp32 with 1 | M and 1 | N elements
@@ -360,7 +367,10 @@ def cutlass_scaled_mm(
         raise RuntimeError("cutlass_scaled_mm: scales must be contiguous")
     if bias is not None and (bias.numel() != N or bias.dtype != out_dtype or not bias.is_contiguous()):
         raise RuntimeError("cutlass_scaled_mm: bias must be a contiguous [N] tensor of out_dtype")
-    out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    elif out.shape != (M, N) or out.dtype != out_dtype or out.stride(1) != 1:
+        raise RuntimeError("cutlass_scaled_mm: out must be a row-major [M, N] tensor of out_dtype")
     lib = _lib.load()
     ws = _mm_workspace(a.device, int(lib.b200_scaled_mm_workspace_bytes(M, N)))
     rc = lib.b200_scaled_mm_fp8(
@@ -414,6 +424,34 @@ def scaled_fp4_quant(
     return output, output_scale.view(torch.float8_e4m3fn)
 
 
+def scaled_fp4_quant_out(input: torch.Tensor, input_global_scale: torch.Tensor, is_sf_swizzled_layout: bool,
+                         output: torch.Tensor, output_scale: torch.Tensor) -> None:
+    """The `.out` overload (torch_bindings.cpp:218-222): caller-allocated packed output [m, out_n/2]
+    and scale buffer (swizzled buffers must be zero-initialised by the caller or are fully
+    rewritten here: every padded SF is stored)."""
+    _require_cuda(input, input_global_scale, output, output_scale)
+    input = input.reshape(1 if input.dim() == 1 else -1, input.shape[-1])
+    m, n = input.shape
+    if n % 16:
+        raise RuntimeError(f"last dim has to be multiple of 16, but got {n}.")
+    if input.dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError(f"input.dtype needs to be fp16 or bf16 but got {input.dtype}.")
+    if output.dtype != torch.uint8 or output.dim() != 2 or output.shape[0] != m or not output.is_contiguous():
+        raise RuntimeError("scaled_fp4_quant.out: output must be contiguous uint8 [m, out_n/2]")
+    out_n = output.shape[1] * 2
+    if out_n < n or out_n % 16:
+        raise RuntimeError("scaled_fp4_quant.out: output width must cover n and be a multiple of 16 elements")
+    need = (round_up(m, 128) * round_up(out_n // 16, 4)) if is_sf_swizzled_layout else m * (out_n // 16)
+    if output_scale.numel() * output_scale.element_size() < need or not output_scale.is_contiguous():
+        raise RuntimeError("scaled_fp4_quant.out: output_scale buffer too small or not contiguous")
+    if not input.is_contiguous():
+        input = input.contiguous()
+    rc = _lib.load().b200_scaled_fp4_quant(
+        output.data_ptr(), output_scale.data_ptr(), input.data_ptr(), input_global_scale.data_ptr(), m, n, out_n,
+        1 if is_sf_swizzled_layout else 0, _dt(input), _stream(input))
+    _lib.check(rc, "scaled_fp4_quant")
+
+
 def cutlass_scaled_fp4_mm(
     a: torch.Tensor,
     b: torch.Tensor,
@@ -421,6 +459,7 @@ def cutlass_scaled_fp4_mm(
     block_scale_b: torch.Tensor,
     alpha: torch.Tensor,
     out_dtype: torch.dtype,
+    out: torch.Tensor | None = None,
 ) -> torch.Tensor:
     """a [M, K/2] u8, b [N, K/2] u8, swizzled e4m3 block scales, alpha fp32 scalar
     (vllm/_custom_ops.py:733-745; checks nvfp4_scaled_mm_kernels.cu:279-347)."""
@@ -451,7 +490,12 @@ def cutlass_scaled_fp4_mm(
         raise RuntimeError("block scales must be contiguous")
     if alpha.dtype != torch.float32:
         raise RuntimeError("alpha must be float32")
-    out = torch.empty((m, n), dtype=out_dtype, device=a.device)
+    if out_dtype not in (torch.bfloat16, torch.float16):
+        raise RuntimeError("cutlass_scaled_fp4_mm: out_dtype must be bfloat16 or float16")
+    if out is None:
+        out = torch.empty((m, n), dtype=out_dtype, device=a.device)
+    elif out.shape != (m, n) or out.dtype != out_dtype or out.stride(1) != 1:
+        raise RuntimeError("cutlass_scaled_fp4_mm: out must be a row-major [M, N] tensor of out_dtype")
     rc = _lib.load().b200_scaled_mm_nvfp4(out.data_ptr(), a.data_ptr(), b.data_ptr(), sa.data_ptr(), sb.data_ptr(),
                                           alpha.data_ptr(), m, n, k, out.stride(0), _DT[out_dtype], _stream(a))
     _lib.check(rc, "cutlass_scaled_fp4_mm")

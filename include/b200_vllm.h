@@ -236,9 +236,12 @@ int b200_scaled_mm_fp8(void* out, const void* a, const void* b,
                        int64_t ldb, int64_t ldc, int a_scales_numel,
                        int b_scales_numel, int out_dtype, void* workspace,
                        size_t workspace_bytes, b200_stream_t stream);
-/* Optional split-K scratch for the decode regime (M <= 128): fp32 [M][N] plus
- * tile counters.  Zero it ONCE after allocation; the kernels leave it zeroed.
- * workspace == NULL disables split-K. */
+/* Stream-K fixup scratch for the decode regime (M <= 256): 1 KB of per-CTA
+ * flags followed by one fp32 [BN][128] partial tile per CTA.  Zero the first
+ * 1 KB ONCE after allocation; the kernels leave the flags zeroed.  Must be
+ * 16-byte aligned and must not be shared by GEMMs running concurrently on
+ * different streams.  workspace == NULL: every CTA takes whole 128-row weight
+ * tiles (no K split), which leaves SMs idle when N/128 < #SMs. */
 size_t b200_scaled_mm_workspace_bytes(int M, int N);
 
 /* ------------------------------------------------------------------------
@@ -279,6 +282,45 @@ int b200_rotary_embedding_neox(void* query, void* key, const int64_t* positions,
                                int rot_dim, int64_t q_stride_tok,
                                int64_t k_stride_tok, int dtype,
                                b200_stream_t stream);
+
+/* ------------------------------------------------------------------------
+ * Fused element-wise neighbours: one launch instead of two or
+ * three, activations touched once.
+ *
+ * b200_rms_norm_dynamic_per_token_quant replaces
+ *   rms_norm_dynamic_per_token_quant
+ *   csrc/libtorch_stable/quantization/fused_kernels/fused_layernorm_dynamic_per_token_quant.cu:50-91,174-230
+ *   math   .../fused_kernels/layernorm_utils.cuh (compute_rms, compute_dynamic_per_token_scales, norm_and_quant)
+ *   schema csrc/libtorch_stable/torch_bindings.cpp:394-396
+ *   x = input (+ residual, fp32; residual <- T(x)); rms = rsqrt(mean(x^2) + eps);
+ *   y = T(T(x * rms) * weight); scale[m] = max(min(amax|y|, ub) / 448, 1/(448*512));
+ *   result = e4m3(y / scale[m]).  result/residual rows are contiguous [hidden].
+ *
+ * b200_silu_and_mul_dynamic_per_token_quant: bit-identical to silu_and_mul
+ *   (csrc/libtorch_stable/activation_kernels.cu) followed by
+ *   dynamic_per_token_scaled_fp8_quant (fp8/common.cu:137-179); input [tokens][2d].
+ *
+ * b200_rotary_embedding_and_cache_write: bit-identical to rotary_embedding (neox,
+ *   csrc/libtorch_stable/pos_encoding_kernels.cu) on query/key in place followed by
+ *   reshape_and_cache_flash of (key, value); the fused entry behind
+ *   AttentionImpl.do_rope_and_kv_cache_update (vllm/v1/attention/backend.py:932-980).
+ *   Tokens t >= num_slots or with slot -1 are rotated but not cached.
+ * ---------------------------------------------------------------------- */
+int b200_rms_norm_dynamic_per_token_quant(void* result, const void* input, const void* weight,
+                                          float* scales, float epsilon, const float* scale_ub,
+                                          void* residual /* nullable, updated in place */,
+                                          int64_t num_tokens, int hidden, int64_t in_row_stride,
+                                          int dtype, b200_stream_t stream);
+int b200_silu_and_mul_dynamic_per_token_quant(void* result, float* scales, const void* input,
+                                              int64_t num_tokens, int d, int dtype,
+                                              b200_stream_t stream);
+int b200_rotary_embedding_and_cache_write(
+    void* query, void* key, const void* value, const int64_t* positions, const void* cos_sin_cache,
+    void* key_cache, void* value_cache, const int64_t* slot_mapping, int64_t num_tokens,
+    int64_t num_slots, int num_q_heads, int num_kv_heads, int head_size, int rot_dim,
+    int64_t q_stride_tok, int64_t k_stride_tok, int64_t v_stride_tok, int block_size,
+    int64_t block_stride, int64_t page_stride, int64_t head_stride, int dtype, int kv_dtype,
+    const float* k_scale, const float* v_scale, int kv_scale_stride, b200_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -323,3 +323,19 @@ def rotary_embedding_neox(positions, q, k, head_size, cos_sin_cache):
         return v.to(t.dtype).reshape(t.shape)
 
     return rot_one(q), rot_one(k)
+
+
+def rms_norm_dynamic_per_token_quant(x, w, eps, scale_ub=None, residual=None):
+    """csrc/libtorch_stable/quantization/fused_kernels/fused_layernorm_dynamic_per_token_quant.cu:50-91 with
+    layernorm_utils.cuh (compute_rms, compute_dynamic_per_token_scales, norm_and_quant): the norm sees the
+    UNROUNDED fp32 sum input + residual (residual <- T(sum)); y = T(T(x * rms) * w); s = max(min(amax|y|, ub) / 448,
+    1/(448*512)); q = e4m3(y / s).  Returns (q, s [M,1], new_residual | None)."""
+    xf = x.float()
+    new_res = None
+    if residual is not None:
+        xf = xf + residual.float()
+        new_res = xf.to(x.dtype)
+    rms = torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)
+    y = ((xf * rms).to(x.dtype).float() * w.float()).to(x.dtype).float()
+    q, s = dynamic_per_token_scaled_fp8_quant(y, scale_ub)
+    return q, s, new_res

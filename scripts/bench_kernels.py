@@ -1,0 +1,229 @@
+#!/usr/bin/env python
+"""Kernel-level roofline sweep on one B200: every hot-path kernel timed alone with CUDA
+events after warm-up, inputs rotated through buffers whose total footprint exceeds the 126 MB L2
+(so no launch finds its operands cached), next to the INSTALLED vLLM wheel's kernels on the same tensors.
+
+  python scripts/bench_kernels.py [--what gemm,attn,elem,nvfp4] [--ref] > gpurun_out/kernels.jsonl
+
+One JSON object per line: {"kernel", "shape", "us", "gbs" | "tflops", "frac_hbm" | "frac_tensor", "ref_us"}.
+Peaks: MEASURED_PEAKS.json (HBM copy GB/s; FP8/FP4 tensor peak taken as 2x / 4x the measured bf16 burst).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import sys
+from pathlib import Path
+
+import torch
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+from vllm_b200 import ops  # noqa: E402
+
+DEV = torch.device("cuda:0")
+PK = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {
+    "hbm_gbs": 6650.0, "bf16_tflops": 1590.0}
+HBM, BF16 = PK["hbm_gbs"], PK["bf16_tflops"]
+
+
+def timeit(fns, reps=20, warm=3):
+    """fns: callables over distinct operand sets.  One pass over all of them is captured into a CUDA graph
+    (so Python / ctypes launch overhead is not what gets timed) and replayed `reps` times.  Returns us per call."""
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(warm):
+            for f in fns:
+                f()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for f in fns:
+            f()
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / (reps * len(fns))
+
+
+def emit(**kw):
+    print(json.dumps(kw), flush=True)
+
+
+def nsets(bytes_per_set, min_total=400e6, cap=16):
+    return int(max(2, min(cap, -(-min_total // bytes_per_set))))
+
+
+def bench_fp8_gemm(ref: bool):
+    try:
+        from vllm import _custom_ops as vops
+    except Exception:
+        vops = None
+    shapes = {"qkv": (4096, 6144), "o": (4096, 4096), "gate_up": (4096, 28672), "down": (14336, 4096)}
+    for M in (16, 64, 128, 256, 1024, 4096, 8192):
+        for name, (K, N) in shapes.items():
+            if M >= 1024 and name in ("o",):
+                continue
+            wbytes = K * N
+            ns = nsets(wbytes + M * K)
+            ws = [(torch.randn(N, K, device=DEV) * 0.05).to(torch.float8_e4m3fn) for _ in range(ns)]
+            xs = [torch.randn(M, K, device=DEV).to(torch.float8_e4m3fn) for _ in range(ns)]
+            a_s = torch.rand(M, 1, device=DEV) + 0.5
+            b_s = torch.rand(1, device=DEV) + 0.5
+            outs = [torch.empty(M, N, dtype=torch.bfloat16, device=DEV) for _ in range(2)]
+            fns = [(lambda i=i: ops.cutlass_scaled_mm(xs[i], ws[i].t(), a_s, b_s, torch.bfloat16, out=outs[i % 2]))
+                   for i in range(ns)]
+            us = timeit(fns, reps=10 if M >= 1024 else 20)
+            byts = K * N + M * K + 2 * M * N
+            fl = 2.0 * M * N * K
+            rec = {"kernel": "fp8_gemm", "layer": name, "M": M, "N": N, "K": K, "us": round(us, 2),
+                   "gbs": round(byts / us / 1e3, 1), "frac_hbm": round(byts / us / 1e3 / HBM, 3),
+                   "tflops": round(fl / us / 1e6, 1), "frac_tensor_fp8": round(fl / us / 1e6 / (2 * BF16), 3)}
+            if ref and vops is not None:
+                try:
+                    rf = [(lambda i=i: vops.cutlass_scaled_mm(xs[i], ws[i].t(), scale_a=a_s, scale_b=b_s,
+                                                              out_dtype=torch.bfloat16)) for i in range(ns)]
+                    rec["ref_us"] = round(timeit(rf, reps=10 if M >= 1024 else 20), 2)
+                except Exception as e:
+                    rec["ref_err"] = repr(e)[:100]
+            emit(**rec)
+            del ws, xs
+
+
+def bench_nvfp4_gemm(ref: bool):
+    try:
+        from vllm import _custom_ops as vops
+    except Exception:
+        vops = None
+    # Llama-3.1-70B TP8 per-GPU shapes + one square
+    shapes = {"qkv": (8192, 1280), "o": (1024, 8192), "gate_up": (8192, 7168), "down": (3584, 8192), "sq": (8192, 8192)}
+    for M in (64, 256, 1024, 4096, 8192):
+        for name, (K, N) in shapes.items():
+            if M < 1024 and name == "sq":
+                continue
+            ns = nsets(K * N // 2 + M * K // 2)
+            gs = torch.tensor([1.0], device=DEV)
+            wq, wsf, xq, xsf = [], [], [], []
+            for _ in range(ns):
+                q, sf = ops.scaled_fp4_quant((torch.randn(N, K, device=DEV) * 0.5).to(torch.bfloat16), gs)
+                wq.append(q); wsf.append(sf)
+                q, sf = ops.scaled_fp4_quant(torch.randn(M, K, device=DEV).to(torch.bfloat16), gs)
+                xq.append(q); xsf.append(sf)
+            alpha = torch.tensor([1.0], device=DEV)
+            outs = [torch.empty(M, N, dtype=torch.bfloat16, device=DEV) for _ in range(2)]
+            fns = [(lambda i=i: ops.cutlass_scaled_fp4_mm(xq[i], wq[i], xsf[i], wsf[i], alpha, torch.bfloat16, out=outs[i % 2]))
+                   for i in range(ns)]
+            us = timeit(fns, reps=10 if M >= 1024 else 20)
+            byts = K * N * 9 // 16 + M * K * 9 // 16 + 2 * M * N
+            fl = 2.0 * M * N * K
+            rec = {"kernel": "nvfp4_gemm", "layer": name, "M": M, "N": N, "K": K, "us": round(us, 2),
+                   "gbs": round(byts / us / 1e3, 1), "frac_hbm": round(byts / us / 1e3 / HBM, 3),
+                   "tflops": round(fl / us / 1e6, 1), "frac_tensor_fp4": round(fl / us / 1e6 / (4 * BF16), 3)}
+            if ref and vops is not None:
+                try:
+                    rf = [(lambda i=i: vops.cutlass_scaled_fp4_mm(xq[i], wq[i], xsf[i], wsf[i], alpha, torch.bfloat16))
+                          for i in range(ns)]
+                    rec["ref_us"] = round(timeit(rf, reps=10 if M >= 1024 else 20), 2)
+                except Exception as e:
+                    rec["ref_err"] = repr(e)[:100]
+            emit(**rec)
+            del wq, wsf, xq, xsf
+
+
+def bench_attention(ref: bool):
+    cases = [  # name, B, ctx, Hq, Hkv, kv dtype
+        ("cfg2 8B bf16 B64 ctx4K TP1", 64, 4096, 32, 8, "auto"),
+        ("cfg3 8B fp8 B128 ctx4K TP1", 128, 4096, 32, 8, "fp8"),
+        ("cfg3 8B fp8 B128 ctx4K TP8", 128, 4096, 4, 1, "fp8"),
+        ("cfg4 70B fp8 B256 ctx8K TP8", 256, 8192, 8, 1, "fp8"),
+        ("cfg5 8B bf16 B16 ctx128K TP8 (shared prefix)", 16, 131072, 4, 1, "auto"),
+        ("ragged 8B bf16 B64 ctx2K-4K", 64, 4096, 32, 8, "auto"),
+    ]
+    D, bs = 128, 16
+    for name, B, ctx, Hq, Hkv, kvd in cases:
+        shared = "shared prefix" in name
+        bps = ctx // bs
+        nb = (bps if shared else B * bps) + 1
+        it = 1 if kvd == "fp8" else 2
+        per_cache = 2 * nb * bs * Hkv * D * it
+        ns = nsets(per_cache, min_total=600e6, cap=8)
+        caches = []
+        for _ in range(ns):
+            if kvd == "fp8":
+                kv = torch.randint(0, 256, (2, nb, bs, Hkv, D), device=DEV, dtype=torch.uint8) & 0x77
+            else:
+                kv = ((torch.rand(2, nb, bs, Hkv, D, device=DEV) * 2 - 1) * D ** -0.5).to(torch.bfloat16)
+            caches.append(kv)
+        if shared:
+            bt = (torch.randperm(nb - 1, device=DEV)[:bps] + 1).to(torch.int32).repeat(B, 1)
+        else:
+            bt = (torch.randperm(nb - 1, device=DEV)[: B * bps] + 1).reshape(B, bps).to(torch.int32)
+        if name.startswith("ragged"):
+            sl = torch.randint(2048, 4097, (B,), device=DEV, dtype=torch.int32)
+        else:
+            sl = torch.full((B,), ctx, device=DEV, dtype=torch.int32)
+        q = torch.randn(B, Hq, D, device=DEV).to(torch.bfloat16)
+        out = torch.empty_like(q)
+        sc = torch.tensor([0.05], device=DEV)
+        splits = ops.paged_decode_num_splits(B, Hq, Hkv, ctx, DEV)
+        wsb = ops.paged_decode_workspace_bytes(B, Hq, D, splits)
+        wsp = torch.empty(max(wsb, 16), dtype=torch.uint8, device=DEV)
+        fns = [(lambda i=i: ops.paged_attention_decode(out, q, caches[i][0], caches[i][1], bt, sl, D ** -0.5, ctx, kvd,
+                                                       sc, sc, num_splits=splits, workspace=wsp)) for i in range(ns)]
+        us = timeit(fns, reps=10)
+        logical = int(sl.sum().item()) * Hkv * D * 2 * it + B * Hq * D * 4
+        unique = (ctx * Hkv * D * 2 * it + B * Hq * D * 4) if shared else logical
+        rec = {"kernel": "paged_decode", "case": name, "splits": splits, "us": round(us, 2),
+               "logical_gbs": round(logical / us / 1e3, 1), "frac_hbm": round(unique / us / 1e3 / HBM, 3),
+               "frac_8TBps": round(unique / us / 1e3 / 8000, 3), "bytes": logical, "unique_bytes": unique}
+        emit(**rec)
+        del caches
+
+
+def bench_elementwise():
+    B, H, I = 128, 4096, 14336
+    x = torch.randn(B, H, device=DEV).to(torch.bfloat16)
+    r = torch.randn(B, H, device=DEV).to(torch.bfloat16)
+    w = torch.ones(H, device=DEV, dtype=torch.bfloat16)
+    gu = torch.randn(B, 2 * I, device=DEV).to(torch.bfloat16)
+    act = torch.empty(B, I, device=DEV, dtype=torch.bfloat16)
+    emit(kernel="fused_add_rms_norm", shape=[B, H], us=round(timeit([lambda: ops.fused_add_rms_norm(x, r, w, 1e-5)], 50), 2))
+    emit(kernel="per_token_fp8_quant", shape=[B, H], us=round(timeit([lambda: ops.scaled_fp8_quant(x, use_per_token_if_dynamic=True)], 50), 2))
+    emit(kernel="per_token_fp8_quant", shape=[B, I], us=round(timeit([lambda: ops.scaled_fp8_quant(act, use_per_token_if_dynamic=True)], 50), 2))
+    emit(kernel="silu_and_mul", shape=[B, I], us=round(timeit([lambda: ops.silu_and_mul(act, gu)], 50), 2))
+    for name in ("rms_norm_fp8_quant", "silu_mul_fp8_quant"):
+        if hasattr(ops, name):
+            if name == "rms_norm_fp8_quant":
+                f = lambda: ops.rms_norm_fp8_quant(x, w, 1e-5, residual=r)
+            else:
+                f = lambda: ops.silu_mul_fp8_quant(gu)
+            emit(kernel=name, us=round(timeit([f], 50), 2))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--what", default="gemm,attn,elem,nvfp4")
+    ap.add_argument("--ref", action="store_true", help="also time the INSTALLED vLLM kernels")
+    a = ap.parse_args()
+    what = set(a.what.split(","))
+    emit(peaks={"hbm_gbs": HBM, "bf16_tflops": BF16, "fp8_peak_used": 2 * BF16, "fp4_peak_used": 4 * BF16},
+         gpu=torch.cuda.get_device_name(0))
+    if "attn" in what:
+        bench_attention(a.ref)
+    if "gemm" in what:
+        bench_fp8_gemm(a.ref)
+    if "nvfp4" in what:
+        bench_nvfp4_gemm(a.ref)
+    if "elem" in what:
+        bench_elementwise()
+
+
+if __name__ == "__main__":
+    main()

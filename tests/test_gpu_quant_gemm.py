@@ -281,3 +281,76 @@ def test_elementwise_companions(ops):
     rq, rk = O.rotary_embedding_neox(pos, q, k, 128, cs)
     torch.testing.assert_close(qd.cpu().float(), rq.float(), atol=2e-2, rtol=1e-2)
     torch.testing.assert_close(kd.cpu().float(), rk.float(), atol=2e-2, rtol=1e-2)
+
+
+# ---------------------------------------------------------------- fused element-wise
+@pytest.mark.parametrize("with_res", [False, True])
+@pytest.mark.parametrize("shape", [(128, 4096), (5, 8192), (3, 1000), (2, 14336)])
+def test_fused_rms_norm_fp8_quant(ops, with_res, shape):
+    """rms_norm_dynamic_per_token_quant vs the oracle restatement of the reference's fused kernel: the
+    residual update is bit-exact; scales agree to fp32 reduction-order noise; codes within 1 fp8 step
+    (the bar of tests/kernels/core/test_fused_quant_layernorm.py)."""
+    M, H = shape
+    g = torch.Generator().manual_seed(M + H)
+    x = torch.randn(M, H, generator=g).to(torch.bfloat16)
+    w = (torch.rand(H, generator=g) + 0.5).to(torch.bfloat16)
+    r = torch.randn(M, H, generator=g).to(torch.bfloat16) if with_res else None
+    rd = r.to(DEV) if with_res else None
+    q, s = ops.rms_norm_dynamic_per_token_quant(x.to(DEV), w.to(DEV), 1e-5, residual=rd)
+    rq, rs, rr = O.rms_norm_dynamic_per_token_quant(x, w, 1e-5, residual=r)
+    if with_res:
+        assert torch.equal(rd.cpu(), rr)
+    torch.testing.assert_close(s.cpu(), rs, rtol=1e-2, atol=0)  # a 1-ulp bf16 flip of the row max moves the scale by < 2^-8
+    deq, rdeq = q.cpu().float() * s.cpu(), rq.float() * rs
+    # 1 fp8 step = 2^-3 relative at most; compare dequantised values
+    assert ((deq - rdeq).abs() <= 0.13 * rdeq.abs() + 2e-2 * rs).all()
+    assert (q.cpu().view(torch.uint8) == rq.view(torch.uint8)).float().mean() > 0.97
+    ub = torch.tensor([0.5])
+    q2, s2 = ops.rms_norm_dynamic_per_token_quant(x.to(DEV), w.to(DEV), 1e-5, scale_ub=ub.to(DEV))
+    assert float(s2.max()) <= 0.5 / 448 * 1.0001
+
+
+@pytest.mark.parametrize("shape", [(128, 14336), (7, 3584), (3, 1000)])
+def test_fused_silu_mul_fp8_quant_is_the_composition(ops, shape):
+    M, d = shape
+    g = torch.Generator().manual_seed(d)
+    gu = (torch.randn(M, 2 * d, generator=g) * 2).to(torch.bfloat16).to(DEV)
+    q, s = ops.silu_and_mul_dynamic_per_token_quant(gu)
+    act = torch.empty(M, d, dtype=torch.bfloat16, device=DEV)
+    ops.silu_and_mul(act, gu)
+    q2, s2 = ops.scaled_fp8_quant(act, use_per_token_if_dynamic=True)
+    assert torch.equal(s, s2) and torch.equal(q.view(torch.uint8), q2.view(torch.uint8))
+    rq, rs = O.dynamic_per_token_scaled_fp8_quant(O.silu_and_mul(gu.cpu()))
+    torch.testing.assert_close(s.cpu(), rs, rtol=1e-2, atol=0)
+
+
+@pytest.mark.parametrize("kv_dtype", ["auto", "fp8"])
+def test_fused_rope_cache_write_is_the_composition(ops, kv_dtype):
+    T, Hq, Hkv, D, bs, nb = 37, 32, 8, 128, 16, 40
+    g = torch.Generator().manual_seed(11)
+    qkv = torch.randn(T + 3, (Hq + 2 * Hkv) * D, generator=g).to(torch.bfloat16)  # rows are slices of the fused qkv buffer
+    pos = torch.randint(0, 4000, (T + 3,), generator=g)
+    inv = 1.0 / (500000.0 ** (torch.arange(0, D, 2).float() / D))
+    cs = torch.cat([torch.outer(torch.arange(4096).float(), inv).cos(), torch.outer(torch.arange(4096).float(), inv).sin()], -1).to(torch.bfloat16)
+    slots = torch.randperm(nb * bs, generator=g)[:T].to(torch.int64)  # fewer slots than rows: CUDA-graph padding
+    slots[4] = -1
+    cdt = torch.uint8 if kv_dtype == "fp8" else torch.bfloat16
+    ks, vs = torch.tensor([0.3]), torch.tensor([0.2])
+
+    def run(fused):
+        buf = qkv.clone().to(DEV)
+        q, k, v = buf.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+        kv = torch.zeros(2, nb, bs, Hkv, D, dtype=cdt, device=DEV)
+        if fused:
+            ops.rotary_embedding_and_cache_write(pos.to(DEV), q, k, v, D, cs.to(DEV), kv[0], kv[1], slots.to(DEV), kv_dtype,
+                                                 ks.to(DEV), vs.to(DEV))
+        else:
+            ops.rotary_embedding(pos.to(DEV), q, k, D, cs.to(DEV))
+            ops.reshape_and_cache_flash(k.view(T + 3, Hkv, D), v.view(T + 3, Hkv, D), kv[0], kv[1], slots.to(DEV), kv_dtype,
+                                        ks.to(DEV), vs.to(DEV))
+        return buf.cpu(), kv.cpu()
+
+    b1, c1 = run(True)
+    b2, c2 = run(False)
+    assert torch.equal(b1, b2) and torch.equal(c1, c2)
+    assert c1.float().abs().sum() > 0

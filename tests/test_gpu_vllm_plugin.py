@@ -129,10 +129,13 @@ def _fp8_kernel(act_key, w_key, n, k):
     from vllm.model_executor.kernels.linear import FP8ScaledMMLinearLayerConfig
     from vllm_b200.linear_kernels import B200FP8ScaledMMLinearKernel
 
+    from vllm.config import VllmConfig, set_current_vllm_config
+
     c = FP8ScaledMMLinearLayerConfig(weight_quant_key=w_key, activation_quant_key=act_key, weight_shape=(n, k),
                                      input_dtype=torch.bfloat16, out_dtype=torch.bfloat16)
     assert B200FP8ScaledMMLinearKernel.is_supported()[0] and B200FP8ScaledMMLinearKernel.can_implement(c)[0]
-    return B200FP8ScaledMMLinearKernel(c, ["weight", "weight_scale", "input_scale", "input_scale_ub"])
+    with set_current_vllm_config(VllmConfig()):  # the base class builds a QuantFP8 CustomOp
+        return B200FP8ScaledMMLinearKernel(c, ["weight", "weight_scale", "input_scale", "input_scale_ub"])
 
 
 @pytest.mark.parametrize("static_act", [False, True])

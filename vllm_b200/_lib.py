@@ -62,6 +62,10 @@ SIGNATURES: dict[str, tuple] = {
     "b200_rms_norm": (i32, [vp, vp, vp, vp, i64, i32, i64, f32, i32, vp]),
     "b200_silu_and_mul": (i32, [vp, vp, i64, i32, i32, vp]),
     "b200_rotary_embedding_neox": (i32, [vp, vp, vp, vp, i64, i32, i32, i32, i32, i64, i64, i32, vp]),
+    "b200_rms_norm_dynamic_per_token_quant": (i32, [vp, vp, vp, vp, f32, vp, vp, i64, i32, i64, i32, vp]),
+    "b200_silu_and_mul_dynamic_per_token_quant": (i32, [vp, vp, vp, i64, i32, i32, vp]),
+    "b200_rotary_embedding_and_cache_write": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, i32, i32, i32, i32,
+                                                    i64, i64, i64, i32, i64, i64, i64, i32, i32, vp, vp, i32, vp]),
 }
 
 _lib: C.CDLL | None = None

@@ -26,6 +26,7 @@ SOURCES = [
     "fp8_quant.cu",
     "nvfp4_quant.cu",
     "merge_elementwise.cu",
+    "fused_quant.cu",
     "fp8_gemm.cu",
     "nvfp4_gemm.cu",
 ]

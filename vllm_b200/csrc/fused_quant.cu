@@ -1,0 +1,340 @@
+// Fused element-wise neighbours of the quantised linears and of the cache write.
+// Each removes one or two launch-bound kernels and an activation round trip per layer:
+//   (1) rms_norm_dynamic_per_token_quant   (fused add +) RMSNorm + FP8 per-token quant
+//         reference: csrc/libtorch_stable/quantization/fused_kernels/fused_layernorm_dynamic_per_token_quant.cu:50-91,
+//         math layernorm_utils.cuh (compute_rms / compute_dynamic_per_token_scales / norm_and_quant),
+//         schema csrc/libtorch_stable/torch_bindings.cpp:394-396
+//   (2) silu_and_mul_dynamic_per_token_quant  SiLU(gate)*up + FP8 per-token quant
+//         = silu_and_mul (csrc/libtorch_stable/activation_kernels.cu) followed by
+//           dynamic_per_token_scaled_fp8_quant (fp8/common.cu:137-179), bit-identical to that composition
+//   (3) rotary_embedding_and_cache_write    neox RoPE on q,k (in place) + K/V cache write over slot_mapping
+//         = the fused path behind AttentionImpl.do_rope_and_kv_cache_update (vllm/v1/attention/backend.py:932-980),
+//           bit-identical to rotary_embedding followed by reshape_and_cache_flash
+// One CTA per token row; the row lives in shared memory between the statistics pass and the convert pass,
+// so HBM/L2 sees every activation once; 16-byte vectors throughout.
+#include "common.cuh"
+
+namespace b200 {
+
+constexpr float kFp8MaxF = 448.f;
+constexpr float kMinScaleF = 1.0f / (448.f * 512.f);
+
+__device__ __forceinline__ uint8_t cvt_e4m3_sat(float x) {
+  const float r = fmaxf(-kFp8MaxF, fminf(x, kFp8MaxF));
+  return (uint8_t)__nv_cvt_float_to_fp8(r, __NV_SATFINITE, __NV_E4M3);
+}
+
+template <bool kMax> __device__ __forceinline__ float block_reduce(float v, float* sh) {
+  v = kMax ? warp_max(v) : warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  __syncthreads();  // sh may still be read from a previous reduction
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  const int nw = (blockDim.x + 31) >> 5;
+  float r = lane < nw ? sh[lane] : 0.f;
+  return kMax ? warp_max(r) : warp_sum(r);
+}
+
+// T x T product rounded to T, as `static_cast<scalar_t>(a) * b` does in the reference
+template <typename T> __device__ __forceinline__ float mul_round(float a, float b) {
+  return to_float(from_float<T>(to_float(from_float<T>(a)) * b));
+}
+
+// ---- (1) ---------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(1024) rms_norm_quant_kernel(uint8_t* __restrict__ out, float* __restrict__ scales,
+                                                              const T* __restrict__ in, const T* __restrict__ w,
+                                                              T* __restrict__ residual,
+                                                              const float* __restrict__ scale_ub, int hidden,
+                                                              int64_t in_stride, float eps) {
+  constexpr int N = 16 / sizeof(T);
+  __shared__ float sh[32];
+  extern __shared__ __align__(16) uint8_t row_buf[];
+  float* rowf = reinterpret_cast<float*>(row_buf);  // x (then y) in fp32
+  const int64_t row = blockIdx.x;
+  const T* src = in + row * in_stride;
+  T* res = residual ? residual + row * (int64_t)hidden : nullptr;
+  uint8_t* dst = out + row * (int64_t)hidden;
+  const bool vec = (hidden % N == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0) &&
+                   (!res || (reinterpret_cast<uintptr_t>(res) & 15) == 0) && ((reinterpret_cast<uintptr_t>(w) & 15) == 0);
+  float ss = 0.f;
+  if (vec) {
+    for (int v = threadIdx.x; v < hidden / N; v += blockDim.x) {
+      uint4 a = *reinterpret_cast<const uint4*>(src + v * N);
+      const T* av = reinterpret_cast<const T*>(&a);
+      float x[N];
+#pragma unroll
+      for (int i = 0; i < N; ++i) x[i] = to_float(av[i]);
+      if (res) {
+        uint4 r = *reinterpret_cast<const uint4*>(res + v * N);
+        const T* rv = reinterpret_cast<const T*>(&r);
+        uint4 o;
+        T* ov = reinterpret_cast<T*>(&o);
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+          x[i] += to_float(rv[i]);  // the norm sees the unrounded fp32 sum (layernorm_utils.cuh compute_rms)
+          ov[i] = from_float<T>(x[i]);
+        }
+        *reinterpret_cast<uint4*>(res + v * N) = o;
+      }
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        rowf[v * N + i] = x[i];
+        ss += x[i] * x[i];
+      }
+    }
+  } else {
+    for (int e = threadIdx.x; e < hidden; e += blockDim.x) {
+      float x = to_float(src[e]);
+      if (res) {
+        x += to_float(res[e]);
+        res[e] = from_float<T>(x);
+      }
+      rowf[e] = x;
+      ss += x * x;
+    }
+  }
+  ss = block_reduce<false>(ss, sh);
+  const float rms = rsqrtf(ss / hidden + eps);
+  float amax = 0.f;
+  for (int e = threadIdx.x; e < hidden; e += blockDim.x) {
+    const float y = mul_round<T>(rowf[e] * rms, to_float(w[e]));
+    rowf[e] = y;
+    amax = fmaxf(amax, fabsf(y));
+  }
+  amax = block_reduce<true>(amax, sh);
+  float s = scale_ub ? fminf(amax, *scale_ub) : amax;
+  s = fmaxf(s / kFp8MaxF, kMinScaleF);
+  if (threadIdx.x == 0) scales[row] = s;
+  if ((hidden & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0) {
+    for (int v = threadIdx.x; v < hidden / 4; v += blockDim.x) {
+      const float4 y = *reinterpret_cast<const float4*>(rowf + v * 4);
+      uint32_t q = cvt_e4m3_sat(__fdiv_rn(y.x, s)) | (cvt_e4m3_sat(__fdiv_rn(y.y, s)) << 8) |
+                   (cvt_e4m3_sat(__fdiv_rn(y.z, s)) << 16) | (cvt_e4m3_sat(__fdiv_rn(y.w, s)) << 24);
+      *reinterpret_cast<uint32_t*>(dst + v * 4) = q;
+    }
+  } else {
+    for (int e = threadIdx.x; e < hidden; e += blockDim.x) dst[e] = cvt_e4m3_sat(__fdiv_rn(rowf[e], s));
+  }
+}
+
+// ---- (2) ---------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(1024) silu_mul_quant_kernel(uint8_t* __restrict__ out, float* __restrict__ scales,
+                                                              const T* __restrict__ in, int d) {
+  constexpr int N = 16 / sizeof(T);
+  __shared__ float sh[32];
+  extern __shared__ __align__(16) uint8_t row_buf[];
+  T* rowt = reinterpret_cast<T*>(row_buf);  // act row in T (what silu_and_mul would have stored)
+  const int64_t row = blockIdx.x;
+  const T* g = in + row * 2 * (int64_t)d;
+  const T* u = g + d;
+  uint8_t* dst = out + row * (int64_t)d;
+  float amax = 0.f;
+  auto act = [](T gv, T uv) {
+    const float x = to_float(gv);
+    const T s = from_float<T>(x / (1.0f + expf(-x)));
+    return from_float<T>(to_float(s) * to_float(uv));
+  };
+  if (d % N == 0) {
+    for (int v = threadIdx.x; v < d / N; v += blockDim.x) {
+      uint4 gr = *reinterpret_cast<const uint4*>(g + v * N), ur = *reinterpret_cast<const uint4*>(u + v * N), orr;
+      const T* gv = reinterpret_cast<const T*>(&gr);
+      const T* uv = reinterpret_cast<const T*>(&ur);
+      T* ov = reinterpret_cast<T*>(&orr);
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        ov[i] = act(gv[i], uv[i]);
+        amax = fmaxf(amax, fabsf(to_float(ov[i])));
+      }
+      *reinterpret_cast<uint4*>(rowt + v * N) = orr;
+    }
+  } else {
+    for (int e = threadIdx.x; e < d; e += blockDim.x) {
+      const T y = act(g[e], u[e]);
+      rowt[e] = y;
+      amax = fmaxf(amax, fabsf(to_float(y)));
+    }
+  }
+  amax = block_reduce<true>(amax, sh);
+  const float s = fmaxf(__fdiv_rn(amax, kFp8MaxF), kMinScaleF);
+  if (threadIdx.x == 0) scales[row] = s;
+  if (d % N == 0 && (reinterpret_cast<uintptr_t>(dst) & (N - 1)) == 0) {
+    for (int v = threadIdx.x; v < d / N; v += blockDim.x) {
+      uint4 yr = *reinterpret_cast<const uint4*>(rowt + v * N);
+      const T* yv = reinterpret_cast<const T*>(&yr);
+      uint8_t q[N];
+#pragma unroll
+      for (int i = 0; i < N; ++i) q[i] = cvt_e4m3_sat(__fdiv_rn(to_float(yv[i]), s));
+      *reinterpret_cast<uint2*>(dst + v * N) = *reinterpret_cast<uint2*>(q);
+    }
+  } else {
+    for (int e = threadIdx.x; e < d; e += blockDim.x) dst[e] = cvt_e4m3_sat(__fdiv_rn(to_float(rowt[e]), s));
+  }
+}
+
+// ---- (3) ---------------------------------------------------------------------------------
+template <int kKv> __device__ __forceinline__ uint8_t kv_to_fp8(float x, float scale) {
+  return (uint8_t)__nv_cvt_float_to_fp8(__fdiv_rn(x, scale), __NV_SATFINITE,
+                                        kKv == B200_KV_FP8_E5M2 ? __NV_E5M2 : __NV_E4M3);
+}
+
+template <typename T, int kKv>
+__global__ void __launch_bounds__(256) rope_cache_kernel(
+    T* __restrict__ q, T* __restrict__ k, const T* __restrict__ v, const int64_t* __restrict__ positions,
+    const T* __restrict__ cos_sin, void* __restrict__ key_cache, void* __restrict__ value_cache,
+    const int64_t* __restrict__ slot_mapping, int64_t num_slots, int num_q_heads, int num_kv_heads, int head_size,
+    int rot_dim, int64_t q_st, int64_t k_st, int64_t v_st, int block_size, int64_t block_stride,
+    int64_t page_stride, int64_t head_stride, const float* __restrict__ k_scale, const float* __restrict__ v_scale,
+    int kv_scale_stride) {
+  using cache_t = typename std::conditional<kKv == B200_KV_AUTO, T, uint8_t>::type;
+  extern __shared__ __align__(16) uint8_t kv_buf[];
+  T* ks = reinterpret_cast<T*>(kv_buf);  // rotated key row [Hkv][D]
+  const int64_t tok = blockIdx.x;
+  const int half = rot_dim / 2;
+  const T* cs = cos_sin + positions[tok] * rot_dim;
+  // stage the key row
+  const int kd = num_kv_heads * head_size;
+  for (int i = threadIdx.x; i < kd; i += blockDim.x) ks[i] = k[tok * k_st + i];
+  __syncthreads();
+  const int total = (num_q_heads + num_kv_heads) * half;
+  for (int i = threadIdx.x; i < total; i += blockDim.x) {
+    const int head = i / half, j = i - head * half;
+    const float c = to_float(cs[j]), s = to_float(cs[half + j]);
+    if (head < num_q_heads) {
+      T* base = q + tok * q_st + (int64_t)head * head_size;
+      const float x = to_float(base[j]), y = to_float(base[half + j]);
+      base[j] = from_float<T>(x * c - y * s);
+      base[half + j] = from_float<T>(y * c + x * s);
+    } else {
+      const int h = head - num_q_heads;
+      T* sb = ks + h * head_size;
+      const float x = to_float(sb[j]), y = to_float(sb[half + j]);
+      const T r0 = from_float<T>(x * c - y * s), r1 = from_float<T>(y * c + x * s);
+      sb[j] = r0;
+      sb[half + j] = r1;
+      T* gb = k + tok * k_st + (int64_t)h * head_size;
+      gb[j] = r0;
+      gb[half + j] = r1;
+    }
+  }
+  __syncthreads();
+  if (tok >= num_slots) return;
+  const int64_t slot = slot_mapping[tok];
+  if (slot < 0) return;  // PAD_SLOT_ID
+  const int64_t dst_base = (slot / block_size) * block_stride + (slot % block_size) * page_stride;
+  for (int i = threadIdx.x; i < 2 * kd; i += blockDim.x) {
+    const int which = i / kd, rem = i - which * kd;
+    const int head = rem / head_size, d = rem - head * head_size;
+    const T x = which ? v[tok * v_st + rem] : ks[rem];
+    cache_t* dst = reinterpret_cast<cache_t*>(which ? value_cache : key_cache) + dst_base + (int64_t)head * head_stride;
+    if constexpr (kKv == B200_KV_AUTO) {
+      dst[d] = x;
+    } else {
+      dst[d] = kv_to_fp8<kKv>(to_float(x), (which ? v_scale : k_scale)[head * kv_scale_stride]);
+    }
+  }
+}
+
+template <typename F> static int dispatch16f(int dtype, const char* what, F&& f) {
+  switch (dtype) {
+    case B200_DT_BF16: return f(__nv_bfloat16());
+    case B200_DT_F16: return f(__half());
+    default: set_error("%s: dtype must be fp16 or bf16", what); return B200_ERR_INVALID_ARG;
+  }
+}
+static int row_threads(int vecs) {
+  int t = (vecs + 31) / 32 * 32;
+  return t < 64 ? 64 : (t > 1024 ? 1024 : t);
+}
+
+}  // namespace b200
+
+extern "C" int b200_rms_norm_dynamic_per_token_quant(void* result, const void* input, const void* weight,
+                                                     float* scales, float epsilon, const float* scale_ub,
+                                                     void* residual, int64_t num_tokens, int hidden,
+                                                     int64_t in_row_stride, int dtype, b200_stream_t stream) {
+  using namespace b200;
+  B200_CHECK_ARG(num_tokens >= 0 && hidden > 0 && hidden <= 49152, B200_ERR_INVALID_ARG,
+                 "rms_norm_dynamic_per_token_quant: bad sizes");
+  if (num_tokens == 0) return 0;
+  B200_CHECK_ARG(result && input && weight && scales, B200_ERR_INVALID_ARG,
+                 "rms_norm_dynamic_per_token_quant: null pointer");
+  return dispatch16f(dtype, "rms_norm_dynamic_per_token_quant", [&](auto tag) {
+    using T = decltype(tag);
+    static bool attr = false;
+    if (!attr) {
+      cudaFuncSetAttribute(rms_norm_quant_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 49152 * 4);
+      attr = true;
+    }
+    const int threads = row_threads(hidden / (int)(16 / sizeof(T)));
+    rms_norm_quant_kernel<T><<<(unsigned)num_tokens, threads, hidden * 4, (cudaStream_t)stream>>>(
+        (uint8_t*)result, scales, (const T*)input, (const T*)weight, (T*)residual, scale_ub, hidden, in_row_stride,
+        epsilon);
+    B200_CHECK_LAUNCH();
+    count_launch();
+    return 0;
+  });
+}
+
+extern "C" int b200_silu_and_mul_dynamic_per_token_quant(void* result, float* scales, const void* input,
+                                                         int64_t num_tokens, int d, int dtype, b200_stream_t stream) {
+  using namespace b200;
+  B200_CHECK_ARG(num_tokens >= 0 && d > 0 && d <= 98304, B200_ERR_INVALID_ARG,
+                 "silu_and_mul_dynamic_per_token_quant: bad sizes");
+  if (num_tokens == 0) return 0;
+  B200_CHECK_ARG(result && scales && input, B200_ERR_INVALID_ARG, "silu_and_mul_dynamic_per_token_quant: null pointer");
+  B200_CHECK_ARG(reinterpret_cast<uintptr_t>(input) % 16 == 0, B200_ERR_ALIGNMENT,
+                 "silu_and_mul_dynamic_per_token_quant: input must be 16-byte aligned");
+  return dispatch16f(dtype, "silu_and_mul_dynamic_per_token_quant", [&](auto tag) {
+    using T = decltype(tag);
+    static bool attr = false;
+    if (!attr) {
+      cudaFuncSetAttribute(silu_mul_quant_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 98304 * 2);
+      attr = true;
+    }
+    const int threads = row_threads(d / (int)(16 / sizeof(T)));
+    silu_mul_quant_kernel<T><<<(unsigned)num_tokens, threads, d * sizeof(T), (cudaStream_t)stream>>>(
+        (uint8_t*)result, scales, (const T*)input, d);
+    B200_CHECK_LAUNCH();
+    count_launch();
+    return 0;
+  });
+}
+
+extern "C" int b200_rotary_embedding_and_cache_write(
+    void* query, void* key, const void* value, const int64_t* positions, const void* cos_sin_cache,
+    void* key_cache, void* value_cache, const int64_t* slot_mapping, int64_t num_tokens, int64_t num_slots,
+    int num_q_heads, int num_kv_heads, int head_size, int rot_dim, int64_t q_stride_tok, int64_t k_stride_tok,
+    int64_t v_stride_tok, int block_size, int64_t block_stride, int64_t page_stride, int64_t head_stride, int dtype,
+    int kv_dtype, const float* k_scale, const float* v_scale, int kv_scale_stride, b200_stream_t stream) {
+  using namespace b200;
+  B200_CHECK_ARG(num_tokens >= 0 && rot_dim > 0 && rot_dim % 2 == 0 && rot_dim <= head_size && block_size > 0 &&
+                     num_q_heads > 0 && num_kv_heads > 0,
+                 B200_ERR_INVALID_ARG, "rotary_embedding_and_cache_write: bad sizes");
+  B200_CHECK_ARG(kv_dtype == B200_KV_AUTO || kv_dtype == B200_KV_FP8_E4M3 || kv_dtype == B200_KV_FP8_E5M2,
+                 B200_ERR_INVALID_ARG, "rotary_embedding_and_cache_write: Unsupported data type of kv cache: %d", kv_dtype);
+  B200_CHECK_ARG(kv_dtype == B200_KV_AUTO || (k_scale && v_scale), B200_ERR_INVALID_ARG,
+                 "rotary_embedding_and_cache_write: fp8 cache needs k_scale and v_scale");
+  if (num_tokens == 0) return 0;
+  B200_CHECK_ARG(query && key && value && positions && cos_sin_cache && key_cache && value_cache && slot_mapping,
+                 B200_ERR_INVALID_ARG, "rotary_embedding_and_cache_write: null pointer");
+  const size_t smem = (size_t)num_kv_heads * head_size * 2;
+  B200_CHECK_ARG(smem <= 48 * 1024, B200_ERR_UNSUPPORTED, "rotary_embedding_and_cache_write: key row too large");
+  return dispatch16f(dtype, "rotary_embedding_and_cache_write", [&](auto tag) {
+    using T = decltype(tag);
+    cudaStream_t s = (cudaStream_t)stream;
+#define B200_RC(KV)                                                                                             \
+  rope_cache_kernel<T, KV><<<(unsigned)num_tokens, 256, smem, s>>>(                                             \
+      (T*)query, (T*)key, (const T*)value, positions, (const T*)cos_sin_cache, key_cache, value_cache,          \
+      slot_mapping, num_slots, num_q_heads, num_kv_heads, head_size, rot_dim, q_stride_tok, k_stride_tok,        \
+      v_stride_tok, block_size, block_stride, page_stride, head_stride, k_scale, v_scale, kv_scale_stride)
+    if (kv_dtype == B200_KV_AUTO) B200_RC(B200_KV_AUTO);
+    else if (kv_dtype == B200_KV_FP8_E4M3) B200_RC(B200_KV_FP8_E4M3);
+    else B200_RC(B200_KV_FP8_E5M2);
+#undef B200_RC
+    B200_CHECK_LAUNCH();
+    count_launch();
+    return 0;
+  });
+}

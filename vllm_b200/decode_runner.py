@@ -4,10 +4,10 @@ This is NOT vLLM's model runner (that stays vLLM's — see INTEGRATION.md); it i
 smallest harness that executes exactly the decode step of SURVEY §3.1 for a Llama-style
 dense model so bench.py / smoke() / tests can time and check the hot path end to end:
 
-  per layer:  fused-add RMSNorm -> FP8 per-token quant -> qkv GEMM -> RoPE ->
-              KV-cache write (slot_mapping) -> paged-attention decode (block_table) ->
-              quant -> o_proj GEMM -> [all-reduce] -> fused-add RMSNorm -> quant ->
-              gate_up GEMM -> SiLU*mul -> quant -> down GEMM -> [all-reduce]
+  per layer:  [fused-add RMSNorm + FP8 per-token quant] -> qkv GEMM -> [RoPE + KV-cache write
+              (slot_mapping)] -> paged-attention decode (block_table) -> quant -> o_proj GEMM ->
+              [all-reduce] -> [fused-add RMSNorm + quant] -> gate_up GEMM -> [SiLU*mul + quant] ->
+              down GEMM -> [all-reduce]          ([..] = one fused launch; fused=False runs them apart)
   then:       final norm -> lm_head (vocab-parallel library GEMM) -> greedy argmax.
 
 Tensor parallelism follows vLLM's sharding (vllm/model_executor/layers/linear.py: QKV /
@@ -53,11 +53,12 @@ class DecodeRunner:
     def __init__(self, shape: ModelShape, batch: int, max_ctx: int, *, block_size: int = 16,
                  kv_cache_dtype: str = "fp8", weight_quant: str = "fp8", tp_size: int = 1, tp_rank: int = 0,
                  device: torch.device | str = "cuda:0", seed: int = 0, num_layers: int | None = None,
-                 tp_group=None):
+                 tp_group=None, fused: bool = True):
         self.s = shape
         self.B, self.max_ctx, self.bs = batch, max_ctx, block_size
         self.kv_dtype, self.wq = kv_cache_dtype, weight_quant
         self.tp, self.rank, self.group = tp_size, tp_rank, tp_group
+        self.fused = fused  # use the fused norm+quant / silu+quant / rope+cache kernels
         self.dev = torch.device(device)
         self.L = num_layers if num_layers is not None else shape.num_layers
         assert shape.num_q_heads % tp_size == 0 and shape.num_kv_heads % tp_size == 0
@@ -161,28 +162,47 @@ class DecodeRunner:
         self.input_ids.copy_(torch.randint(0, self.s.vocab, (self.B,), device=self.dev, generator=g))
         ops.compute_slot_mapping(self.query_start_loc, self.positions, self.block_table, self.bs, self.slot_mapping)
 
+    def _mm_fp8(self, xq: torch.Tensor, xs: torch.Tensor, lw) -> torch.Tensor:
+        return ops.cutlass_scaled_mm(xq, lw["w"].t(), xs, lw["s"], self.dtype)
+
     def step_eager(self) -> torch.Tensor:
         s, B = self.s, self.B
         hidden = self.embed[self.input_ids]
         residual = torch.zeros_like(hidden)
         attn_out = torch.empty(B, self.Hq, self.D, device=self.dev, dtype=self.dtype)
+        fused = self.wq == "fp8" and self.fused
         for lw, kv in zip(self.layers, self.kv_caches):
-            ops.fused_add_rms_norm(hidden, residual, lw["ln1"], s.rms_eps)
-            qkv = self._linear(hidden, lw["qkv"])
-            q, k, v = qkv.split([self.Hq * self.D, self.Hkv * self.D, self.Hkv * self.D], dim=-1)
-            ops.rotary_embedding(self.positions, q, k, self.D, self.cos_sin)
             kc, vc = kv.unbind(0)
-            ops.reshape_and_cache_flash(k.view(B, self.Hkv, self.D), v.view(B, self.Hkv, self.D), kc, vc,
-                                        self.slot_mapping, self.kv_dtype, self.k_scale, self.v_scale)
+            if fused:
+                # 10 launches per layer: norm+quant, GEMM, rope+cache, attention (+combine), quant, GEMM,
+                # norm+quant, GEMM, silu*mul+quant, GEMM
+                xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, lw["ln1"], s.rms_eps, residual=residual)
+                qkv = self._mm_fp8(xq, xs, lw["qkv"])
+                q, k, v = qkv.split([self.Hq * self.D, self.Hkv * self.D, self.Hkv * self.D], dim=-1)
+                ops.rotary_embedding_and_cache_write(self.positions, q, k, v, self.D, self.cos_sin, kc, vc,
+                                                     self.slot_mapping, self.kv_dtype, self.k_scale, self.v_scale)
+            else:
+                ops.fused_add_rms_norm(hidden, residual, lw["ln1"], s.rms_eps)
+                qkv = self._linear(hidden, lw["qkv"])
+                q, k, v = qkv.split([self.Hq * self.D, self.Hkv * self.D, self.Hkv * self.D], dim=-1)
+                ops.rotary_embedding(self.positions, q, k, self.D, self.cos_sin)
+                ops.reshape_and_cache_flash(k.view(B, self.Hkv, self.D), v.view(B, self.Hkv, self.D), kc, vc,
+                                            self.slot_mapping, self.kv_dtype, self.k_scale, self.v_scale)
             ops.paged_attention_decode(attn_out, q.view(B, self.Hq, self.D), kc, vc, self.block_table, self.seq_lens,
                                        self.scale, self.max_ctx, self.kv_dtype, self.k_scale, self.v_scale,
                                        num_splits=self.num_splits, workspace=self.attn_ws)
             hidden = self._all_reduce(self._linear(attn_out.view(B, -1), lw["o"]))
-            ops.fused_add_rms_norm(hidden, residual, lw["ln2"], s.rms_eps)
-            gu = self._linear(hidden, lw["gate_up"])
-            act = torch.empty(B, self.inter, device=self.dev, dtype=self.dtype)
-            ops.silu_and_mul(act, gu)
-            hidden = self._all_reduce(self._linear(act, lw["down"]))
+            if fused:
+                xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, lw["ln2"], s.rms_eps, residual=residual)
+                gu = self._mm_fp8(xq, xs, lw["gate_up"])
+                aq, a_s = ops.silu_and_mul_dynamic_per_token_quant(gu)
+                hidden = self._all_reduce(self._mm_fp8(aq, a_s, lw["down"]))
+            else:
+                ops.fused_add_rms_norm(hidden, residual, lw["ln2"], s.rms_eps)
+                gu = self._linear(hidden, lw["gate_up"])
+                act = torch.empty(B, self.inter, device=self.dev, dtype=self.dtype)
+                ops.silu_and_mul(act, gu)
+                hidden = self._all_reduce(self._linear(act, lw["down"]))
         ops.fused_add_rms_norm(hidden, residual, self.final_ln, s.rms_eps)
         logits = torch.matmul(hidden, self.lm_head.t())  # plain library GEMM (bf16 lm_head, as in vLLM)
         if self.tp == 1:

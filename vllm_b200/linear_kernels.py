@@ -24,6 +24,12 @@ from vllm.model_executor.kernels.linear import (
 )
 
 from . import ops
+from . import torch_ops  # noqa: F401  (defines torch.ops.b200.*)
+
+# vLLM traces the model forward with torch.compile (Dynamo): raw ctypes calls are not traceable, so the
+# kernel classes go through the torch.ops.b200.* custom ops (opaque, mutation-annotated, with fake impls),
+# exactly like the reference's classes go through torch.ops._C.*.
+_B = torch.ops.b200
 
 
 def _is_sm100(compute_capability: int | None) -> tuple[bool, str | None]:
@@ -83,10 +89,16 @@ class B200FP8ScaledMMLinearKernel(FP8ScaledMMLinearKernel):
         x2 = x.reshape(-1, x.shape[-1])
         out_dtype = self.config.out_dtype or x.dtype
         if x2.dtype != self.fp8_dtype:
+            xq = torch.empty(x2.shape, dtype=self.fp8_dtype, device=x2.device)
             if self._act_static:
-                xq, xs = ops.scaled_fp8_quant(x2, x_s)
+                xs = x_s
+                _B.static_scaled_fp8_quant(xq, x2, xs)
+            elif self._act_per_token:
+                xs = torch.empty((x2.shape[0], 1), dtype=torch.float32, device=x2.device)
+                _B.dynamic_per_token_scaled_fp8_quant(xq, x2, xs, x_s_ub)
             else:
-                xq, xs = ops.scaled_fp8_quant(x2, None, scale_ub=x_s_ub, use_per_token_if_dynamic=self._act_per_token)
+                xs = torch.empty(1, dtype=torch.float32, device=x2.device)
+                _B.dynamic_scaled_fp8_quant(xq, x2, xs)
         else:
             xq, xs = x2, x_s
         return self.apply_scaled_mm(A=xq, B=w, out_dtype=out_dtype, As=xs, Bs=w_s, bias=bias,
@@ -94,7 +106,8 @@ class B200FP8ScaledMMLinearKernel(FP8ScaledMMLinearKernel):
 
     def apply_scaled_mm(self, *, A: torch.Tensor, B: torch.Tensor, out_dtype: torch.dtype, As: torch.Tensor,
                         Bs: torch.Tensor, bias: torch.Tensor | None, output_shape: list) -> torch.Tensor:
-        out = ops.cutlass_scaled_mm(A, B, As.reshape(-1), Bs.reshape(-1), out_dtype, bias)
+        out = torch.empty((A.shape[0], B.shape[1]), dtype=out_dtype, device=A.device)
+        _B.cutlass_scaled_mm(out, A, B, As.reshape(-1), Bs.reshape(-1), bias)
         return out.view(*output_shape)
 
 
@@ -120,8 +133,13 @@ class B200NvFp4LinearKernel(NvFp4LinearKernel):
     def apply_weights(self, layer: torch.nn.Module, x: torch.Tensor, bias: torch.Tensor | None = None) -> torch.Tensor:
         n = layer.output_size_per_partition
         x2 = x.reshape(-1, x.shape[-1])
-        xq, xsf = ops.scaled_fp4_quant(x2, layer.input_global_scale_inv, is_sf_swizzled_layout=True)
-        out = ops.cutlass_scaled_fp4_mm(xq, layer.weight, xsf, layer.weight_scale, layer.alpha, x.dtype)
+        m, k = x2.shape
+        xq = torch.empty((m, k // 2), dtype=torch.uint8, device=x2.device)
+        # swizzled SF buffer [ru(m,128), ru(k/16,4)] e4m3; the quant kernel writes every padded entry
+        xsf = torch.empty((ops.round_up(m, 128), ops.round_up(k // 16, 4)), dtype=torch.uint8, device=x2.device)
+        _B.scaled_fp4_quant.out(x2, layer.input_global_scale_inv, True, output=xq, output_scale=xsf)
+        out = torch.empty((m, layer.weight.shape[0]), dtype=x.dtype, device=x2.device)
+        _B.cutlass_scaled_fp4_mm(out, xq, layer.weight, xsf, layer.weight_scale, layer.alpha)
         if out.shape[1] != n:
             out = out[:, :n].contiguous()
         if bias is not None:

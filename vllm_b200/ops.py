@@ -320,16 +320,22 @@ _mm_workspaces: dict[tuple[int, int], torch.Tensor] = {}
 
 
 def _mm_workspace(device: torch.device, nbytes: int) -> torch.Tensor | None:
-    """Zero-initialised split-K scratch, one per device (GEMMs of one process are issued on one
-    stream at a time, like vLLM's worker); kernels leave it zeroed."""
+    """Stream-K fixup scratch of the decode-regime GEMM (flags zero-initialised once; the kernels
+    leave them zeroed).  One buffer per (device, stream): GEMMs on one stream are serialised, GEMMs
+    on different streams must not share partials."""
     if nbytes <= 0:
         return None
-    key = (device.index or 0, 0)
+    key = (device.index or 0, torch.cuda.current_stream(device).cuda_stream)
     ws = _mm_workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         if torch.cuda.is_current_stream_capturing():
-            return None  # never allocate/zero inside a capture: split-K is simply skipped
-        ws = torch.zeros(max(nbytes, 8 << 20), dtype=torch.uint8, device=device)
+            # never allocate/zero inside a capture: fall back to the capture-origin stream's buffer if any,
+            # else run without stream-K (whole tiles per CTA)
+            for (d, _), w in _mm_workspaces.items():
+                if d == (device.index or 0) and w.numel() >= nbytes:
+                    return w
+            return None
+        ws = torch.zeros(max(nbytes, 24 << 20), dtype=torch.uint8, device=device)
         _mm_workspaces[key] = ws
     return ws
 
@@ -543,6 +549,78 @@ def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Te
         q.data_ptr(), k.data_ptr(), positions.data_ptr(), cos_sin_cache.data_ptr(), T, q.shape[1] // head_size,
         k.shape[1] // head_size, head_size, cos_sin_cache.shape[1], q.stride(0), k.stride(0), _dt(q), _stream(q))
     _lib.check(rc, "rotary_embedding")
+
+
+def rms_norm_dynamic_per_token_quant(input: torch.Tensor, weight: torch.Tensor, epsilon: float,
+                                     scale_ub: torch.Tensor | None = None, residual: torch.Tensor | None = None,
+                                     output: torch.Tensor | None = None, scales: torch.Tensor | None = None,
+                                     ) -> tuple[torch.Tensor, torch.Tensor]:
+    """(fused add +) RMSNorm + FP8 per-token quant, vllm/_custom_ops.py rms_norm_dynamic_per_token_quant
+    (schema torch_bindings.cpp:394-396).  residual (if given) is updated in place.  Returns (e4m3 [M, H], scales [M, 1])."""
+    _require_cuda(input, weight, scale_ub, residual, output, scales)
+    x = input.reshape(-1, input.shape[-1])
+    if x.stride(-1) != 1:
+        raise RuntimeError("Input must be contiguous in the last dimension")
+    if weight.dtype != x.dtype or (residual is not None and (residual.dtype != x.dtype or not residual.is_contiguous())):
+        raise RuntimeError("rms_norm_dynamic_per_token_quant: weight/residual dtype must match input; residual contiguous")
+    M, H = x.shape
+    if output is None:
+        output = torch.empty((M, H), device=x.device, dtype=FP8_DTYPE)
+    elif output.dtype != FP8_DTYPE or not output.is_contiguous():
+        raise RuntimeError("rms_norm_dynamic_per_token_quant: output must be contiguous float8_e4m3fn")
+    if scales is None:
+        scales = torch.empty((M, 1), device=x.device, dtype=torch.float32)
+    rc = _lib.load().b200_rms_norm_dynamic_per_token_quant(
+        output.data_ptr(), x.data_ptr(), weight.data_ptr(), scales.data_ptr(), float(epsilon), _ptr(scale_ub),
+        _ptr(residual), M, H, x.stride(0), _dt(x), _stream(x))
+    _lib.check(rc, "rms_norm_dynamic_per_token_quant")
+    return output, scales
+
+
+def silu_and_mul_dynamic_per_token_quant(input: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+    """SiLU(x[:, :d]) * x[:, d:] then dynamic per-token FP8 quant in one launch (bit-identical to
+    silu_and_mul + scaled_fp8_quant(use_per_token_if_dynamic=True))."""
+    _require_cuda(input)
+    x = input.reshape(-1, input.shape[-1])
+    if not x.is_contiguous():
+        raise RuntimeError("silu_and_mul_dynamic_per_token_quant: contiguous input expected")
+    M, d = x.shape[0], x.shape[1] // 2
+    out = torch.empty((M, d), device=x.device, dtype=FP8_DTYPE)
+    scales = torch.empty((M, 1), device=x.device, dtype=torch.float32)
+    rc = _lib.load().b200_silu_and_mul_dynamic_per_token_quant(out.data_ptr(), scales.data_ptr(), x.data_ptr(), M, d,
+                                                               _dt(x), _stream(x))
+    _lib.check(rc, "silu_and_mul_dynamic_per_token_quant")
+    return out, scales
+
+
+def rotary_embedding_and_cache_write(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                                     value: torch.Tensor, head_size: int, cos_sin_cache: torch.Tensor,
+                                     key_cache: torch.Tensor, value_cache: torch.Tensor, slot_mapping: torch.Tensor,
+                                     kv_cache_dtype: str, k_scale: torch.Tensor, v_scale: torch.Tensor,
+                                     is_neox: bool = True) -> None:
+    """RoPE on query/key in place + KV-cache write in one launch (the fused op behind
+    AttentionImpl.do_rope_and_kv_cache_update, vllm/v1/attention/backend.py:932-980)."""
+    _require_cuda(positions, query, key, value, cos_sin_cache, key_cache, value_cache, slot_mapping)
+    if not is_neox:
+        raise RuntimeError("rotary_embedding_and_cache_write: only the neox layout is built")
+    T = positions.numel()
+    q, k, v = query.reshape(T, -1), key.reshape(T, -1), value.reshape(T, -1)
+    if q.stride(1) != 1 or k.stride(1) != 1 or v.stride(1) != 1 or key_cache.stride(3) != 1:
+        raise RuntimeError("rotary_embedding_and_cache_write: innermost dimensions must be contiguous")
+    if key_cache.stride() != value_cache.stride():
+        raise RuntimeError("rotary_embedding_and_cache_write: key and value cache strides must match")
+    if slot_mapping.dtype != torch.int64 or not slot_mapping.is_contiguous():
+        raise RuntimeError("slot_mapping must be a contiguous int64 tensor")
+    hkv = k.shape[1] // head_size
+    if k_scale.numel() not in (1, hkv) or k_scale.shape != v_scale.shape:
+        raise RuntimeError("k_scale and v_scale must be of shape [1] or [num_heads]")
+    rc = _lib.load().b200_rotary_embedding_and_cache_write(
+        q.data_ptr(), k.data_ptr(), v.data_ptr(), positions.data_ptr(), cos_sin_cache.data_ptr(), key_cache.data_ptr(),
+        value_cache.data_ptr(), slot_mapping.data_ptr(), T, slot_mapping.numel(), q.shape[1] // head_size, hkv,
+        head_size, cos_sin_cache.shape[1], q.stride(0), k.stride(0), v.stride(0), key_cache.size(1),
+        key_cache.stride(0), key_cache.stride(1), key_cache.stride(2), _dt(q), kv_dtype_code(kv_cache_dtype),
+        k_scale.data_ptr(), v_scale.data_ptr(), 1 if k_scale.numel() > 1 else 0, _stream(q))
+    _lib.check(rc, "rotary_embedding_and_cache_write")
 
 
 def swizzle_blockscale(scale: torch.Tensor) -> torch.Tensor:

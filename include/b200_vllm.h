@@ -236,9 +236,9 @@ int b200_scaled_mm_fp8(void* out, const void* a, const void* b,
                        int64_t ldb, int64_t ldc, int a_scales_numel,
                        int b_scales_numel, int out_dtype, void* workspace,
                        size_t workspace_bytes, b200_stream_t stream);
-/* Stream-K fixup scratch for the decode regime (M <= 256): 1 KB of per-CTA
- * flags followed by one fp32 [BN][128] partial tile per CTA.  Zero the first
- * 1 KB ONCE after allocation; the kernels leave the flags zeroed.  Must be
+/* Split-K / stream-K fix-up scratch for the decode regime (M <= 256): 2 KB of
+ * per-CTA flags followed by one fp32 [BN][128] partial tile per CTA.  Zero the
+ * first 2 KB ONCE after allocation; the kernels leave the flags zeroed.  Must be
  * 16-byte aligned and must not be shared by GEMMs running concurrently on
  * different streams.  workspace == NULL: every CTA takes whole 128-row weight
  * tiles (no K split), which leaves SMs idle when N/128 < #SMs. */
@@ -321,6 +321,16 @@ int b200_rotary_embedding_and_cache_write(
     int64_t q_stride_tok, int64_t k_stride_tok, int64_t v_stride_tok, int block_size,
     int64_t block_stride, int64_t page_stride, int64_t head_stride, int dtype, int kv_dtype,
     const float* k_scale, const float* v_scale, int kv_scale_stride, b200_stream_t stream);
+
+/* -------------------------------------------------------------------------
+ * Debug aid (no reference counterpart): when set to a device buffer of
+ * [grid][16] uint64, the decode-regime scaled_mm kernel stamps %globaltimer at its
+ * phase boundaries (scripts/prof_gemm.py --trace).  Pass NULL to switch it off.
+ * ---------------------------------------------------------------------- */
+void b200_debug_gemm_trace(unsigned long long* device_buffer);
+/* Force the decode-regime work partition (tests / tuning): 0 whole tiles, 1 stream-K and 2 split-K
+ * through the workspace, 3 cluster split-K over distributed shared memory, -1 automatic. */
+void b200_debug_gemm_mode(int mode);
 
 #ifdef __cplusplus
 }

@@ -61,13 +61,13 @@ def nsets(bytes_per_set, min_total=400e6, cap=16):
     return int(max(2, min(cap, -(-min_total // bytes_per_set))))
 
 
-def bench_fp8_gemm(ref: bool):
+def bench_fp8_gemm(ref: bool, ms=(16, 64, 128, 256, 1024, 4096, 8192)):
     try:
         from vllm import _custom_ops as vops
     except Exception:
         vops = None
     shapes = {"qkv": (4096, 6144), "o": (4096, 4096), "gate_up": (4096, 28672), "down": (14336, 4096)}
-    for M in (16, 64, 128, 256, 1024, 4096, 8192):
+    for M in ms:
         for name, (K, N) in shapes.items():
             if M >= 1024 and name in ("o",):
                 continue
@@ -211,6 +211,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--what", default="gemm,attn,elem,nvfp4")
     ap.add_argument("--ref", action="store_true", help="also time the INSTALLED vLLM kernels")
+    ap.add_argument("--ms", default="16,64,128,256,1024,4096,8192")
     a = ap.parse_args()
     what = set(a.what.split(","))
     emit(peaks={"hbm_gbs": HBM, "bf16_tflops": BF16, "fp8_peak_used": 2 * BF16, "fp4_peak_used": 4 * BF16},
@@ -218,7 +219,7 @@ def main():
     if "attn" in what:
         bench_attention(a.ref)
     if "gemm" in what:
-        bench_fp8_gemm(a.ref)
+        bench_fp8_gemm(a.ref, tuple(int(x) for x in a.ms.split(',')))
     if "nvfp4" in what:
         bench_nvfp4_gemm(a.ref)
     if "elem" in what:

@@ -91,6 +91,40 @@ def test_fp8_gemm(ops, mnk, per_token, per_channel, use_bias):
     torch.testing.assert_close(out.cpu().float(), ref, atol=2e-2 * ref.abs().max().item() / 10 + 1e-2, rtol=1e-2)
 
 
+DECODE_MNK = [(1, 256, 128), (16, 4096, 4096), (40, 1008, 1024), (128, 6144, 4096), (128, 384, 2048),
+              (200, 4096, 14336), (256, 640, 512)]
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
+@pytest.mark.parametrize("mnk", DECODE_MNK)
+def test_fp8_gemm_decode_partitions(ops, mnk, mode):
+    """Every work partition of the decode-regime kernel (whole tiles / stream-K / split-K through the
+    workspace / cluster split-K over DSMEM) against the oracle, odd tile counts and ragged N included;
+    each must also be run-to-run deterministic (fixed summation order, no atomics on data)."""
+    from vllm_b200 import _lib
+
+    M, N, K = mnk
+    g = torch.Generator().manual_seed(M * 11 + N + mode)
+    a = torch.randn(M, K, generator=g).to(torch.float8_e4m3fn)
+    b = torch.randn(N, K, generator=g).to(torch.float8_e4m3fn)
+    sa = torch.rand(M, 1, generator=g) * 0.1 + 0.01
+    sb = torch.rand(1, N, generator=g) * 0.1 + 0.01
+    bias = (torch.rand(N, generator=g) * 5).to(torch.bfloat16)
+    lib = _lib.load()
+    lib.b200_debug_gemm_mode(mode)
+    try:
+        args = (a.to(DEV), b.to(DEV).t(), sa.to(DEV), sb.to(DEV), torch.bfloat16, bias.to(DEV))
+        out = ops.cutlass_scaled_mm(*args)
+        again = [ops.cutlass_scaled_mm(*args) for _ in range(3)]
+        torch.cuda.synchronize()
+    finally:
+        lib.b200_debug_gemm_mode(-1)
+    ref = O.scaled_mm(a, b.t(), sa, sb, torch.float32, bias.float())
+    torch.testing.assert_close(out.cpu().float(), ref, atol=2e-2 * ref.abs().max().item() / 10 + 1e-2, rtol=1e-2)
+    for o in again:
+        assert torch.equal(o, out)
+
+
 def test_fp8_gemm_golden_and_fp16_out(ops):
     for case in load_golden("scaled_mm.pt"):
         a = case["a"].view(torch.float8_e4m3fn).to(DEV)

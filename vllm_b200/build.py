@@ -9,6 +9,7 @@ from __future__ import annotations
 import concurrent.futures as cf
 import hashlib
 import os
+import shlex
 import shutil
 import subprocess
 import sys
@@ -28,6 +29,7 @@ SOURCES = [
     "merge_elementwise.cu",
     "fused_quant.cu",
     "fp8_gemm.cu",
+    "fp8_gemm_decode.cu",
     "nvfp4_gemm.cu",
 ]
 
@@ -36,6 +38,7 @@ NVCC_FLAGS = [
     "-std=c++17", "-O3", "-lineinfo",
     "--expt-relaxed-constexpr", "--extended-lambda",
     "-Xcompiler", "-fPIC",
+    *shlex.split(os.environ.get("B200_NVCC_EXTRA", "")),  # experiments: -DB200_EXP_... switches
 ]
 
 

@@ -61,6 +61,12 @@ __device__ __forceinline__ float warp_sum(float v) {
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
+// 1024-byte aligned start of the dynamic shared memory.  Plain pointer arithmetic on the __shared__ array,
+// so the compiler keeps the shared address space (LDS/STS); a round trip through uintptr_t makes every
+// access through the result a generic LD/ST, ~2x the latency and ordered against all other memory ops.
+__device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* raw) {
+  return raw + ((1024u - (smem_u32(raw) & 1023u)) & 1023u);
+}
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }

@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   using Cfg = GemmCfg<BN>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1024(smem_raw);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full_bar = empty_bar + STAGES;
@@ -260,250 +260,6 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
 }
 
 
-// ===================================================================================
-// Decode-regime kernel: persistent, stream-K, swap-AB.
-// ===================================================================================
-template <int BN> struct DecCfg {
-  static constexpr int X_BYTES = 128 * kBK;  // weights
-  static constexpr int Y_BYTES = BN * kBK;   // tokens
-  static constexpr int STAGE_BYTES = X_BYTES + Y_BYTES;
-  static constexpr int STAGES = (196 * 1024) / STAGE_BYTES > 10 ? 10 : (196 * 1024) / STAGE_BYTES;
-  static constexpr int ACC_COLS = BN < 32 ? 32 : BN;  // columns per accumulator buffer
-  static constexpr int TMEM_COLS = 2 * ACC_COLS;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/;
-};
-
-struct DecArgs {
-  void* out;
-  const float* a_scales;  // per token (M) or [1]
-  const float* b_scales;  // per channel (N) or [1]
-  const void* bias;       // [N] out dtype or null
-  float* partials;        // [gridDim.x][BN][128] fp32 stream-K partials (null: whole tiles only)
-  int* flags;             // [gridDim.x], zero between launches
-  int64_t ldc;
-  int M, N, K;
-  int a_scales_numel, b_scales_numel;
-  int num_tiles, num_kb;  // ceil(N/128), ceil(K/128)
-};
-
-__device__ __forceinline__ int ld_acquire(const int* p) {
-  int v;
-  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release(int* p, int v) {
-  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
-
-// unit range of CTA c: units are (tile-major) u = tile * num_kb + kb
-__device__ __forceinline__ void cta_range(const DecArgs& g, int c, int P, long long& u0, long long& u1) {
-  if (g.partials) {
-    const long long U = (long long)g.num_tiles * g.num_kb;
-    u0 = U * c / P;
-    u1 = U * (c + 1) / P;
-  } else {  // no workspace: whole tiles only
-    u0 = ((long long)g.num_tiles * c / P) * g.num_kb;
-    u1 = ((long long)g.num_tiles * (c + 1) / P) * g.num_kb;
-  }
-}
-
-template <int BN, typename OutT>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-    fp8_gemm_decode_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_a,
-                           const DecArgs g) {
-  using Cfg = DecCfg<BN>;
-  constexpr int STAGES = Cfg::STAGES;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + STAGES;
-  uint64_t* tmem_full_bar = empty_bar + STAGES;  // [2]
-  uint64_t* tmem_empty_bar = tmem_full_bar + 2;  // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int P = gridDim.x, c = blockIdx.x;
-  long long u0, u1;
-  cta_range(g, c, P, u0, u1);
-  const int KB = g.num_kb;
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
-    }
-    for (int b = 0; b < 2; ++b) {
-      mbar_init(&tmem_full_bar[b], 1);
-      mbar_init(&tmem_empty_bar[b], 4);  // one arrive per epilogue warp
-    }
-    fence_barrier_init();
-    prefetch_tensormap(&tmap_w);
-    prefetch_tensormap(&tmap_a);
-  }
-  if (warp == 1) umma::tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
-  umma::fence_before_sync();
-  __syncthreads();
-  umma::fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;
-
-  if (warp == 0) {
-    // ===== TMA producer: one continuous stream of (weights, tokens) stages across segments =====
-    if (umma::elect_one()) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (long long u = u0; u < u1; ++u) {
-        const int tile = (int)(u / KB), kb = (int)(u - (long long)tile * KB);
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sx = smem + stage * Cfg::STAGE_BYTES;
-        mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
-        tma_load_2d(sx, &tmap_w, &full_bar[stage], kb * kBK, tile * 128, kEvictFirst);       // streamed once
-        tma_load_2d(sx + Cfg::X_BYTES, &tmap_a, &full_bar[stage], kb * kBK, 0, kEvictLast);  // re-read by every CTA
-        if (++stage == STAGES) {
-          stage = 0;
-          phase ^= 1;
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (umma::elect_one()) {
-      constexpr uint32_t idesc = umma::make_idesc_f8(128, BN);
-      int stage = 0;
-      uint32_t phase = 0;
-      int seg = 0;
-      for (long long u = u0; u < u1; ++seg) {
-        const int kb0 = (int)(u % KB);
-        const int nkb = (int)min((long long)(KB - kb0), u1 - u);
-        const int buf = seg & 1;
-        mbar_wait(&tmem_empty_bar[buf], (((uint32_t)seg >> 1) & 1) ^ 1);  // epilogue drained this accumulator
-        umma::fence_after_sync();
-        const uint32_t tacc = tmem_base + buf * Cfg::ACC_COLS;
-        for (int kb = 0; kb < nkb; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          umma::fence_after_sync();
-          const uint32_t sx = smem_u32(smem + stage * Cfg::STAGE_BYTES);
-          const uint64_t dx = umma::make_desc_k_sw128(sx);
-          const uint64_t dy = umma::make_desc_k_sw128(sx + Cfg::X_BYTES);
-#pragma unroll
-          for (int kk = 0; kk < kBK / 32; ++kk)
-            umma::mma_f8f6f4(tacc, umma::desc_advance(dx, kk * 32), umma::desc_advance(dy, kk * 32), idesc,
-                             (kb | kk) != 0);
-          umma::commit(&empty_bar[stage]);
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1;
-          }
-        }
-        umma::commit(&tmem_full_bar[buf]);
-        u += nkb;
-      }
-    }
-  } else {
-    // ===== epilogue warps: warp w owns TMEM lanes 32*(w%4) .. +31 (= weight rows of the tile) =====
-    const int q = warp & 3;
-    const int et = q * 32 + lane;  // 0..127 within the epilogue group == TMEM lane == weight row in tile
-    OutT* outp = reinterpret_cast<OutT*>(g.out);
-    const OutT* bias = reinterpret_cast<const OutT*>(g.bias);
-    int seg = 0;
-    for (long long u = u0; u < u1; ++seg) {
-      const int tile = (int)(u / KB), kb0 = (int)(u - (long long)tile * KB);
-      const int nkb = (int)min((long long)(KB - kb0), u1 - u);
-      const int buf = seg & 1;
-      const bool is_head = (kb0 == 0), is_full = is_head && nkb == KB;
-      const int n = tile * 128 + et;  // weight row = output column
-      mbar_wait(&tmem_full_bar[buf], ((uint32_t)seg >> 1) & 1);
-      umma::fence_after_sync();
-      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + buf * Cfg::ACC_COLS;
-      if (!is_head) {
-        // ---- tail part of a tile: emit the raw fp32 partial, column-major so every store is coalesced
-        float* ws = g.partials + ((size_t)c * BN) * 128 + et;
-#pragma unroll 1
-        for (int j0 = 0; j0 < BN; j0 += 16) {
-          uint32_t r[16];
-          umma::ld_32x32b_x16(tacc + j0, r);
-          umma::ld_wait();
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (j0 + j < g.M) ws[(size_t)(j0 + j) * 128] = __uint_as_float(r[j]);
-        }
-        umma::fence_before_sync();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
-        __threadfence();
-        epi_bar();
-        if (et == 0) st_release(g.flags + c, 1);
-      } else {
-        // ---- head part (or the whole K range): gather the tail owners' partials, scale, store
-        int c_last = c;
-        if (!is_full) {
-          const long long U = (long long)g.num_tiles * KB;
-          const long long last_unit = (long long)(tile + 1) * KB - 1;
-          // owner of unit x is the largest cc with U*cc/P <= x
-          c_last = (int)(((last_unit + 1) * P - 1) / U);
-          while (U * (c_last + 1) / P <= last_unit) ++c_last;
-          while (U * c_last / P > last_unit) --c_last;
-          if (et == 0) {
-            for (int cc = c + 1; cc <= c_last; ++cc) {
-              uint32_t spins = 0;
-              while (ld_acquire(g.flags + cc) == 0) {
-                if (++spins > (1u << 26)) {
-                  printf("b200: stream-K fixup wait timed out (cta %d waits for %d)\n", c, cc);
-                  __trap();
-                }
-              }
-            }
-          }
-          epi_bar();
-        }
-        float sx_row = 1.f, bias_row = 0.f;
-        if (n < g.N) {
-          sx_row = g.b_scales[g.b_scales_numel > 1 ? n : 0];
-          if (bias) bias_row = to_float(bias[n]);
-        }
-#pragma unroll 1
-        for (int j0 = 0; j0 < BN; j0 += 16) {
-          uint32_t r[16];
-          umma::ld_32x32b_x16(tacc + j0, r);
-          umma::ld_wait();
-          if (j0 >= g.M) continue;
-          float v[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-          for (int cc = c + 1; cc <= c_last; ++cc) {
-            const float* ws = g.partials + ((size_t)cc * BN + j0) * 128 + et;
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (j0 + j < g.M) v[j] += __ldcg(ws + (size_t)j * 128);
-          }
-          if (n < g.N) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int m = j0 + j;
-              if (m < g.M) {
-                const float as = g.a_scales[g.a_scales_numel > 1 ? m : 0];
-                outp[(int64_t)m * g.ldc + n] = from_float<OutT>(v[j] * as * sx_row + bias_row);
-              }
-            }
-          }
-        }
-        umma::fence_before_sync();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);
-        if (!is_full) {
-          epi_bar();  // every thread has consumed the partials
-          if (et == 0)
-            for (int cc = c + 1; cc <= c_last; ++cc) g.flags[cc] = 0;
-        }
-      }
-      u += nkb;
-    }
-  }
-  umma::fence_before_sync();
-  __syncthreads();
-  if (warp == 1) umma::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
-}
-
 // ---- host side ------------------------------------------------------------------
 struct Tmap2Key {
   const void* base;
@@ -564,25 +320,11 @@ static int launch_fp8_gemm(const CUtensorMap& tx, const CUtensorMap& ty, const G
   return 0;
 }
 
-template <int BN, typename OutT>
-static int launch_fp8_decode(const CUtensorMap& tw, const CUtensorMap& ta, const DecArgs& d, dim3 grid,
-                             cudaStream_t stream) {
-  using Cfg = DecCfg<BN>;
-  auto kern = fp8_gemm_decode_kernel<BN, OutT>;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (e != cudaSuccess) {
-      set_error("fp8 decode gemm: cudaFuncSetAttribute(%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
-      return B200_ERR_CUDA;
-    }
-    attr = true;
-  }
-  kern<<<grid, kGemmThreads, Cfg::SMEM_BYTES, stream>>>(tw, ta, d);
-  B200_CHECK_LAUNCH();
-  count_launch();
-  return 0;
-}
+// decode regime (M <= 256): fp8_gemm_decode.cu
+template <typename OutT>
+int run_fp8_decode(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
+                   const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc, int a_scales_numel,
+                   int b_scales_numel, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 
 template <typename OutT>
 static int run_fp8_gemm(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
@@ -604,49 +346,9 @@ static int run_fp8_gemm(void* out, const void* a, const void* b, const float* a_
   g.splitk_cnt = nullptr;
   const int total_kb = (K + kBK - 1) / kBK;
   g.k_blocks_per_split = total_kb;
-  if (M <= 256) {
-    // ---- decode regime: persistent stream-K, swap-AB
-    const int bn = M <= 16 ? 16 : (M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256)));
-    CUtensorMap tw, ta;
-    int rc;
-    if ((rc = get_kmajor_tmap(&tw, b, N, K, ldb, 128))) return rc;
-    if ((rc = get_kmajor_tmap(&ta, a, M, K, lda, bn))) return rc;
-    DecArgs d;
-    d.out = out;
-    d.a_scales = a_scales;
-    d.b_scales = b_scales;
-    d.bias = bias;
-    d.ldc = ldc;
-    d.M = M;
-    d.N = N;
-    d.K = K;
-    d.a_scales_numel = a_scales_numel;
-    d.b_scales_numel = b_scales_numel;
-    d.num_tiles = (N + 127) / 128;
-    d.num_kb = total_kb;
-    const long long units = (long long)d.num_tiles * d.num_kb;
-    int P = sm_count();
-    const size_t need = b200_scaled_mm_workspace_bytes(M, N);
-    const bool have_ws = workspace && workspace_bytes >= need && reinterpret_cast<uintptr_t>(workspace) % 16 == 0;
-    if (have_ws) {
-      // at least 4 k-blocks per CTA so the fixed prologue/epilogue cost is amortised
-      if (units / 4 < P) P = (int)(units / 4 > 0 ? units / 4 : 1);
-      d.flags = reinterpret_cast<int*>(workspace);
-      d.partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + 1024);
-    } else {
-      if (d.num_tiles < P) P = d.num_tiles;
-      d.flags = nullptr;
-      d.partials = nullptr;
-    }
-    dim3 grid(P, 1, 1);
-    switch (bn) {
-      case 16: return launch_fp8_decode<16, OutT>(tw, ta, d, grid, stream);
-      case 32: return launch_fp8_decode<32, OutT>(tw, ta, d, grid, stream);
-      case 64: return launch_fp8_decode<64, OutT>(tw, ta, d, grid, stream);
-      case 128: return launch_fp8_decode<128, OutT>(tw, ta, d, grid, stream);
-      default: return launch_fp8_decode<256, OutT>(tw, ta, d, grid, stream);
-    }
-  }
+  if (M <= 256)
+    return run_fp8_decode<OutT>(out, a, b, a_scales, b_scales, bias, M, N, K, lda, ldb, ldc, a_scales_numel,
+                                b_scales_numel, workspace, workspace_bytes, stream);
   CUtensorMap tx, ty;
   int rc;
   const int bn = (N % 256 == 0 || N > 2048) ? 256 : 128;
@@ -658,18 +360,6 @@ static int run_fp8_gemm(void* out, const void* a, const void* b, const float* a_
 }
 
 }  // namespace b200
-
-extern "C" size_t b200_scaled_mm_workspace_bytes(int M, int N) {
-  // stream-K fixup scratch of the decode regime (M <= 256): 1 KB of per-CTA flags, then one fp32
-  // [BN][128] partial per CTA.  Zero the first 1 KB ONCE after allocation; the kernels leave the
-  // flags zeroed.  One workspace must not be shared by GEMMs running concurrently on two streams.
-  (void)N;
-  if (M > 256 || M <= 0) return 0;
-  const int bn = M <= 16 ? 16 : (M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256)));
-  int P = b200::sm_count();
-  if (P > 256) P = 256;
-  return 1024 + (size_t)P * bn * 128 * 4;
-}
 
 extern "C" int b200_scaled_mm_fp8(void* out, const void* a, const void* b, const float* a_scales,
                                   const float* b_scales, const void* bias, int M, int N, int K, int64_t lda,

@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
   constexpr int KS = D / 16;  // k-steps of QK^T == 16-wide d groups of PV
 
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1024(smem_raw);
   constexpr int kDataBytes = Cfg::RING_BYTES > Cfg::EPI_BYTES ? Cfg::RING_BYTES : Cfg::EPI_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kDataBytes);
 

@@ -323,6 +323,15 @@ int b200_rotary_embedding_and_cache_write(
     const float* k_scale, const float* v_scale, int kv_scale_stride, b200_stream_t stream);
 
 /* -------------------------------------------------------------------------
+ * Programmatic dependent launch (no reference counterpart).  On by default (B200_PDL=0 in the
+ * environment or b200_set_pdl(0) turns it off): every kernel is launched so that the next kernel's
+ * prologue overlaps this kernel's tail, and every kernel waits for its predecessors' memory before
+ * touching global data.  Results are identical either way.
+ * ---------------------------------------------------------------------- */
+void b200_set_pdl(int enabled);
+int b200_get_pdl(void);
+
+/* -------------------------------------------------------------------------
  * Debug aid (no reference counterpart): when set to a device buffer of
  * [grid][16] uint64, the decode-regime scaled_mm kernel stamps %globaltimer at its
  * phase boundaries (scripts/prof_gemm.py --trace).  Pass NULL to switch it off.

@@ -37,6 +37,8 @@ __global__ void __launch_bounds__(256) cache_write_kernel(
     int block_size, int64_t key_stride, int64_t value_stride, int64_t block_stride, int64_t page_stride,
     int64_t head_stride, const float* __restrict__ k_scale, const float* __restrict__ v_scale,
     int kv_scale_stride) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   using cache_t = typename std::conditional<kKv == B200_KV_AUTO, scalar_t, uint8_t>::type;
   constexpr int kVec = 16 / sizeof(scalar_t);  // source elements per 16-byte vector
   const int64_t token = blockIdx.x;
@@ -106,6 +108,8 @@ __global__ void __launch_bounds__(256) slot_mapping_kernel(int64_t* __restrict__
                                                            int num_reqs, const int64_t* __restrict__ positions,
                                                            const int32_t* __restrict__ block_table,
                                                            int64_t block_table_stride, int block_size) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   // blockIdx.x < num_reqs: one request each; blockIdx.x == num_reqs: padding tail.
   if ((int)blockIdx.x == num_reqs) {
     for (int64_t t = num_tokens + threadIdx.x; t < num_slots; t += blockDim.x) slot_mapping[t] = -1;
@@ -131,7 +135,7 @@ static int launch_cache_write(const void* key, const void* value, void* key_cach
   int threads = work < 32 ? 32 : (work > 256 ? 256 : ((work + 31) / 32) * 32);
   dim3 grid((unsigned)num_tokens), block(threads);
 #define B200_CW(KV)                                                                                          \
-  cache_write_kernel<scalar_t, KV><<<grid, block, 0, stream>>>(                                              \
+  launch_kernel(cache_write_kernel<scalar_t, KV>, dim3(grid), dim3(block), 0, stream, 1,                                               \
       (const scalar_t*)key, (const scalar_t*)value, key_cache, value_cache, slot_mapping, num_heads,        \
       head_size, block_size, key_stride, value_stride, block_stride, page_stride, head_stride, k_scale,     \
       v_scale, kv_scale_stride)
@@ -197,7 +201,7 @@ extern "C" int b200_compute_slot_mapping(int64_t* slot_mapping, int64_t num_slot
   if (num_slots == 0) return 0;
   B200_CHECK_ARG(slot_mapping && query_start_loc && positions && block_table, B200_ERR_INVALID_ARG,
                  "compute_slot_mapping: null pointer");
-  slot_mapping_kernel<<<num_reqs + 1, 256, 0, (cudaStream_t)stream>>>(
+  launch_kernel(slot_mapping_kernel, dim3(num_reqs + 1), dim3(256), 0, (cudaStream_t)stream, 1, 
       slot_mapping, num_slots, num_tokens, query_start_loc, num_reqs, positions, block_table, block_table_stride, block_size);
   B200_CHECK_LAUNCH();
   count_launch();

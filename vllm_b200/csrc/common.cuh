@@ -35,6 +35,45 @@ void count_launch(int n = 1);
 
 int sm_count();
 
+// ---- launch helper: programmatic dependent launch (PDL) ---------------------------------------
+// Every kernel of this library is launched with the programmatic-stream-serialization attribute, so the
+// NEXT kernel on the stream may be scheduled while this one drains: its CTAs run their prologue (barrier
+// init, TMEM allocation, descriptor prefetch, weight prefetch) and then block in pdl_wait() until all
+// memory effects of the preceding grid are visible.  The rule each kernel follows: no global-memory access
+// that depends on, or could race with, an earlier kernel before pdl_wait().  Kernels that do not belong to
+// this library never trigger early, so mixing with them degenerates to ordinary stream order.
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                 int cluster_x, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[2];
+  int n = 0;
+  if (cluster_x > 1) {
+    at[n].id = cudaLaunchAttributeClusterDimension;
+    at[n].val.clusterDim.x = cluster_x;
+    at[n].val.clusterDim.y = 1;
+    at[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  if (pdl_enabled()) {
+    at[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  cfg.attrs = at;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---- scalar conversions --------------------------------------------------
 template <typename T> __device__ __forceinline__ float to_float(T v);
 template <> __device__ __forceinline__ float to_float<float>(float v) { return v; }

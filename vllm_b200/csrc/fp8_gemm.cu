@@ -119,6 +119,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1)
   __syncthreads();
   umma::fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();
+  pdl_wait();  // setup above overlapped the previous kernel's tail
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -314,7 +316,7 @@ static int launch_fp8_gemm(const CUtensorMap& tx, const CUtensorMap& ty, const G
     }
     attr = true;
   }
-  kern<<<grid, kGemmThreads, Cfg::SMEM_BYTES, stream>>>(tx, ty, g);
+  launch_kernel(kern, dim3(grid), dim3(kGemmThreads), Cfg::SMEM_BYTES, stream, 1, tx, ty, g);
   B200_CHECK_LAUNCH();
   count_launch();
   return 0;

@@ -206,6 +206,7 @@ __global__ void __launch_bounds__(kDecThreads, 1)
   cluster_range(g, cid, split, NC, u0, u1);
   const int KB = g.num_kb;
 
+  pdl_trigger();
   if (threadIdx.x == 0) {
     trace_stamp(g, TR_ENTRY);
     for (int s = 0; s < STAGES; ++s) {
@@ -231,19 +232,31 @@ __global__ void __launch_bounds__(kDecThreads, 1)
     // ===== TMA producer =====
     if (umma::elect_one()) {
       trace_stamp(g, TR_SETUP);
-      int stage = 0;
-      uint32_t phase = 0;
-      for (long long u = u0; u < u1; ++u) {
-        if (u == u0 + STAGES) trace_stamp(g, TR_FILLED);
+      auto load_w = [&](long long u, int stage) {
         const int st = (int)(u / KB), kb = (int)(u - (long long)st * KB);
-        const int tile = 2 * st + rank;
-        mbar_wait(&empty_bar[stage], phase ^ 1);
-        uint8_t* sx = smem + stage * Cfg::STAGE_BYTES;
         mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
-        tma_load_2d(sx, &tmap_w, &full_bar[stage], kb * kDBK, tile * 128, kEvictFirst);  // streamed once
+        tma_load_2d(smem + stage * Cfg::STAGE_BYTES, &tmap_w, &full_bar[stage], kb * kDBK, (2 * st + rank) * 128,
+                    kEvictFirst);  // streamed once
+      };
+      auto load_a = [&](long long u, int stage) {
+        const int kb = (int)(u % KB);
         // my half of the token tile, delivered to both CTAs of the pair
-        tma_load_2d_mc(sx + Cfg::X_BYTES + rank * (Cfg::Y_BYTES / 2), &tmap_a, &full_bar[stage], kb * kDBK,
-                       rank * (BN / 2), pair_mask, kEvictLast);
+        tma_load_2d_mc(smem + stage * Cfg::STAGE_BYTES + Cfg::X_BYTES + rank * (Cfg::Y_BYTES / 2), &tmap_a,
+                       &full_bar[stage], kb * kDBK, rank * (BN / 2), pair_mask, kEvictLast);
+      };
+      // The weights do not depend on the preceding kernel: fill the ring with them while it drains, and
+      // only then wait for the activations (programmatic dependent launch).
+      const int pre = (int)min((long long)STAGES, u1 - u0);
+      for (int i = 0; i < pre; ++i) load_w(u0 + i, i);
+      pdl_wait();
+      for (int i = 0; i < pre; ++i) load_a(u0 + i, i);
+      int stage = pre == STAGES ? 0 : pre;
+      uint32_t phase = pre == STAGES ? 1 : 0;
+      for (long long u = u0 + pre; u < u1; ++u) {
+        if (u == u0 + STAGES) trace_stamp(g, TR_FILLED);
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        load_w(u, stage);
+        load_a(u, stage);
         if (++stage == STAGES) {
           stage = 0;
           phase ^= 1;
@@ -300,6 +313,7 @@ __global__ void __launch_bounds__(kDecThreads, 1)
     const int m_cols = min(BN, (g.M + 15) & ~15);  // token columns that can be non-zero (multiple of 16)
     const int nch = m_cols >> 4;
     uint32_t fix_phase = 0;
+    pdl_wait();  // scales, bias, workspace and the output buffer belong to the stream order from here
     for (int j = eid; j < BN; j += 256) s_as[j] = j < g.M ? g.a_scales[g.a_scales_numel > 1 ? j : 0] : 0.f;
     epi_bar();
     // Scale, convert and store one finished chunk (16 tokens x this thread's weight row).  One warp per
@@ -642,13 +656,18 @@ static int launch_fp8_decode(const CUtensorMap& tw, const CUtensorMap& ta, const
   cfg.blockDim = dim3(kDecThreads, 1, 1);
   cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
   cfg.stream = stream;
-  cudaLaunchAttribute at[1];
+  cudaLaunchAttribute at[2];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = cluster_size;
   at[0].val.clusterDim.y = 1;
   at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
+  if (pdl_enabled() && !max_active_out) {
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.numAttrs = 2;
+  }
   if (max_active_out) {  // query only: how many clusters of this size are co-resident
     int n = 0;
     cudaError_t qe = cudaOccupancyMaxActiveClusters(&n, kern, &cfg);

@@ -43,6 +43,8 @@ __global__ void __launch_bounds__(256) per_token_quant_kernel(uint8_t* __restric
                                                               const T* __restrict__ in,
                                                               const float* __restrict__ scale_ub, int hidden,
                                                               int64_t in_stride, int64_t out_stride) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   __shared__ float sh[8];
   constexpr int N = Vec16<T>::N;
   const int64_t row = blockIdx.x;
@@ -99,6 +101,8 @@ __global__ void __launch_bounds__(256) per_token_quant_kernel(uint8_t* __restric
 template <typename T>
 __global__ void __launch_bounds__(256) tensor_amax_kernel(float* __restrict__ scale, const T* __restrict__ in,
                                                           int hidden, int64_t in_stride) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   __shared__ float sh[8];
   constexpr int N = Vec16<T>::N;
   const T* src = in + (int64_t)blockIdx.x * in_stride;
@@ -124,6 +128,8 @@ __global__ void __launch_bounds__(256) scaled_quant_kernel(uint8_t* __restrict__
                                                            const float* __restrict__ scale, int hidden,
                                                            int64_t in_stride, int64_t out_stride, int group_m,
                                                            int group_n, int64_t ss_i, int64_t ss_j) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   constexpr int N = Vec16<T>::N;
   const int64_t row = blockIdx.x;
   const T* src = in + row * in_stride;
@@ -171,7 +177,7 @@ extern "C" int b200_static_scaled_fp8_quant(void* out, const void* input, const 
   B200_CHECK_ARG(out && input && scale, B200_ERR_INVALID_ARG, "static_scaled_fp8_quant: null pointer");
   return dispatch_dtype(dtype, [&](auto tag) {
     using T = decltype(tag);
-    scaled_quant_kernel<T><<<(unsigned)num_tokens, 256, 0, (cudaStream_t)stream>>>(
+    launch_kernel(scaled_quant_kernel<T>, dim3((unsigned)num_tokens), dim3(256), 0, (cudaStream_t)stream, 1, 
         (uint8_t*)out, (const T*)input, scale, hidden, in_row_stride, out_row_stride, group_m, group_n,
         scale_stride_i, scale_stride_j);
     B200_CHECK_LAUNCH();
@@ -195,9 +201,9 @@ extern "C" int b200_dynamic_scaled_fp8_quant(void* out, const void* input, float
   B200_CHECK_ARG(out && input, B200_ERR_INVALID_ARG, "dynamic_scaled_fp8_quant: null pointer");
   return dispatch_dtype(dtype, [&](auto tag) {
     using T = decltype(tag);
-    tensor_amax_kernel<T><<<(unsigned)num_tokens, 256, 0, s>>>(scale, (const T*)input, hidden, in_row_stride);
+    launch_kernel(tensor_amax_kernel<T>, dim3((unsigned)num_tokens), dim3(256), 0, s, 1, scale, (const T*)input, hidden, in_row_stride);
     B200_CHECK_LAUNCH();
-    scaled_quant_kernel<T><<<(unsigned)num_tokens, 256, 0, s>>>((uint8_t*)out, (const T*)input, scale, hidden,
+    launch_kernel(scaled_quant_kernel<T>, dim3((unsigned)num_tokens), dim3(256), 0, s, 1, (uint8_t*)out, (const T*)input, scale, hidden,
                                                                in_row_stride, out_row_stride, (int)num_tokens,
                                                                hidden, 0, 0);
     B200_CHECK_LAUNCH();
@@ -220,10 +226,10 @@ extern "C" int b200_dynamic_per_token_scaled_fp8_quant(void* out, const void* in
     cudaStream_t s = (cudaStream_t)stream;
     const int threads = hidden / N >= 256 ? 256 : (hidden / N > 32 ? ((hidden / N + 31) / 32) * 32 : 32);
     if (hidden <= 4 * 256 * N)
-      per_token_quant_kernel<T, 4><<<(unsigned)num_tokens, threads, 0, s>>>(
+      launch_kernel(per_token_quant_kernel<T, 4>, dim3((unsigned)num_tokens), dim3(threads), 0, s, 1, 
           (uint8_t*)out, scales, (const T*)input, scale_ub, hidden, in_row_stride, out_row_stride);
     else
-      per_token_quant_kernel<T, 0><<<(unsigned)num_tokens, threads, 0, s>>>(
+      launch_kernel(per_token_quant_kernel<T, 0>, dim3((unsigned)num_tokens), dim3(threads), 0, s, 1, 
           (uint8_t*)out, scales, (const T*)input, scale_ub, hidden, in_row_stride, out_row_stride);
     B200_CHECK_LAUNCH();
     count_launch();

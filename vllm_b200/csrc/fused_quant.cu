@@ -47,6 +47,8 @@ __global__ void __launch_bounds__(1024) rms_norm_quant_kernel(uint8_t* __restric
                                                               T* __restrict__ residual,
                                                               const float* __restrict__ scale_ub, int hidden,
                                                               int64_t in_stride, float eps) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   constexpr int N = 16 / sizeof(T);
   __shared__ float sh[32];
   extern __shared__ __align__(16) uint8_t row_buf[];
@@ -122,6 +124,8 @@ __global__ void __launch_bounds__(1024) rms_norm_quant_kernel(uint8_t* __restric
 template <typename T>
 __global__ void __launch_bounds__(1024) silu_mul_quant_kernel(uint8_t* __restrict__ out, float* __restrict__ scales,
                                                               const T* __restrict__ in, int d) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   constexpr int N = 16 / sizeof(T);
   __shared__ float sh[32];
   extern __shared__ __align__(16) uint8_t row_buf[];
@@ -187,6 +191,8 @@ __global__ void __launch_bounds__(256) rope_cache_kernel(
     int rot_dim, int64_t q_st, int64_t k_st, int64_t v_st, int block_size, int64_t block_stride,
     int64_t page_stride, int64_t head_stride, const float* __restrict__ k_scale, const float* __restrict__ v_scale,
     int kv_scale_stride) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   using cache_t = typename std::conditional<kKv == B200_KV_AUTO, T, uint8_t>::type;
   extern __shared__ __align__(16) uint8_t kv_buf[];
   T* ks = reinterpret_cast<T*>(kv_buf);  // rotated key row [Hkv][D]
@@ -268,7 +274,7 @@ extern "C" int b200_rms_norm_dynamic_per_token_quant(void* result, const void* i
       attr = true;
     }
     const int threads = row_threads(hidden / (int)(16 / sizeof(T)));
-    rms_norm_quant_kernel<T><<<(unsigned)num_tokens, threads, hidden * 4, (cudaStream_t)stream>>>(
+    launch_kernel(rms_norm_quant_kernel<T>, dim3((unsigned)num_tokens), dim3(threads), hidden * 4, (cudaStream_t)stream, 1, 
         (uint8_t*)result, scales, (const T*)input, (const T*)weight, (T*)residual, scale_ub, hidden, in_row_stride,
         epsilon);
     B200_CHECK_LAUNCH();
@@ -294,7 +300,7 @@ extern "C" int b200_silu_and_mul_dynamic_per_token_quant(void* result, float* sc
       attr = true;
     }
     const int threads = row_threads(d / (int)(16 / sizeof(T)));
-    silu_mul_quant_kernel<T><<<(unsigned)num_tokens, threads, d * sizeof(T), (cudaStream_t)stream>>>(
+    launch_kernel(silu_mul_quant_kernel<T>, dim3((unsigned)num_tokens), dim3(threads), d * sizeof(T), (cudaStream_t)stream, 1, 
         (uint8_t*)result, scales, (const T*)input, d);
     B200_CHECK_LAUNCH();
     count_launch();
@@ -325,7 +331,7 @@ extern "C" int b200_rotary_embedding_and_cache_write(
     using T = decltype(tag);
     cudaStream_t s = (cudaStream_t)stream;
 #define B200_RC(KV)                                                                                             \
-  rope_cache_kernel<T, KV><<<(unsigned)num_tokens, 256, smem, s>>>(                                             \
+  launch_kernel(rope_cache_kernel<T, KV>, dim3((unsigned)num_tokens), dim3(256), smem, s, 1,                                              \
       (T*)query, (T*)key, (const T*)value, positions, (const T*)cos_sin_cache, key_cache, value_cache,          \
       slot_mapping, num_slots, num_q_heads, num_kv_heads, head_size, rot_dim, q_stride_tok, k_stride_tok,        \
       v_stride_tok, block_size, block_stride, page_stride, head_stride, k_scale, v_scale, kv_scale_stride)

@@ -14,6 +14,8 @@ __global__ void __launch_bounds__(128) merge_states_kernel(
     T* __restrict__ out, float* __restrict__ out_lse, const T* __restrict__ p_out, const float* __restrict__ p_lse,
     const T* __restrict__ s_out, const float* __restrict__ s_lse, int64_t num_tokens, int num_heads, int head_size,
     int64_t o_st, int64_t o_sh, int64_t p_st, int64_t p_sh, int64_t s_st, int64_t s_sh, int64_t lse_sh) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   constexpr int N = 16 / sizeof(T);
   const int packs = head_size / N;
   const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -64,6 +66,8 @@ template <typename T>
 __global__ void __launch_bounds__(256) rms_norm_kernel(T* __restrict__ out, const T* __restrict__ in,
                                                        const T* __restrict__ w, T* __restrict__ residual,
                                                        int hidden, int64_t in_stride, float eps) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   __shared__ float sh[8];
   extern __shared__ __align__(16) uint8_t row_buf[];  // fp32 copy of the row
   float* rowf = reinterpret_cast<float*>(row_buf);
@@ -91,6 +95,8 @@ __global__ void __launch_bounds__(256) rms_norm_kernel(T* __restrict__ out, cons
 
 template <typename T>
 __global__ void __launch_bounds__(256) silu_and_mul_kernel(T* __restrict__ out, const T* __restrict__ in, int d) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   constexpr int N = 16 / sizeof(T);
   const int64_t row = blockIdx.x;
   const T* g = in + row * 2 * (int64_t)d;
@@ -126,6 +132,8 @@ __global__ void __launch_bounds__(256) rope_neox_kernel(T* __restrict__ q, T* __
                                                         const T* __restrict__ cos_sin, int num_q_heads,
                                                         int num_kv_heads, int head_size, int rot_dim,
                                                         int64_t q_st, int64_t k_st) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   const int64_t tok = blockIdx.x;
   const int half = rot_dim / 2;
   const T* cs = cos_sin + positions[tok] * rot_dim;
@@ -175,7 +183,7 @@ extern "C" int b200_merge_attn_states(void* output, float* output_lse, const voi
                        al(suffix_output, s_stride_tok, s_stride_head),
                    B200_ERR_ALIGNMENT, "merge_attn_states: tensors must be 16-byte aligned");
     const int64_t total = num_tokens * num_heads * (head_size / N);
-    merge_states_kernel<T><<<(unsigned)((total + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+    launch_kernel(merge_states_kernel<T>, dim3((unsigned)((total + 127) / 128)), dim3(128), 0, (cudaStream_t)stream, 1, 
         (T*)output, output_lse, (const T*)prefix_output, prefix_lse, (const T*)suffix_output, suffix_lse, num_tokens,
         num_heads, head_size, out_stride_tok, out_stride_head, p_stride_tok, p_stride_head, s_stride_tok,
         s_stride_head, lse_stride_head);
@@ -198,7 +206,7 @@ extern "C" int b200_rms_norm(void* out, const void* input, const void* weight, v
       cudaFuncSetAttribute(rms_norm_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768 * 4);
       attr = true;
     }
-    rms_norm_kernel<T><<<(unsigned)num_tokens, 256, hidden * 4, (cudaStream_t)stream>>>(
+    launch_kernel(rms_norm_kernel<T>, dim3((unsigned)num_tokens), dim3(256), hidden * 4, (cudaStream_t)stream, 1, 
         (T*)out, (const T*)input, (const T*)weight, (T*)residual, hidden, in_row_stride, eps);
     B200_CHECK_LAUNCH();
     count_launch();
@@ -214,7 +222,7 @@ extern "C" int b200_silu_and_mul(void* out, const void* input, int64_t num_token
   B200_CHECK_ARG(out && input, B200_ERR_INVALID_ARG, "silu_and_mul: null pointer");
   return dispatch16(dtype, "silu_and_mul", [&](auto tag) {
     using T = decltype(tag);
-    silu_and_mul_kernel<T><<<(unsigned)num_tokens, 256, 0, (cudaStream_t)stream>>>((T*)out, (const T*)input, d);
+    launch_kernel(silu_and_mul_kernel<T>, dim3((unsigned)num_tokens), dim3(256), 0, (cudaStream_t)stream, 1, (T*)out, (const T*)input, d);
     B200_CHECK_LAUNCH();
     count_launch();
     return 0;
@@ -232,7 +240,7 @@ extern "C" int b200_rotary_embedding_neox(void* query, void* key, const int64_t*
   B200_CHECK_ARG(query && key && positions && cos_sin_cache, B200_ERR_INVALID_ARG, "rotary_embedding: null pointer");
   return dispatch16(dtype, "rotary_embedding", [&](auto tag) {
     using T = decltype(tag);
-    rope_neox_kernel<T><<<(unsigned)num_tokens, 256, 0, (cudaStream_t)stream>>>(
+    launch_kernel(rope_neox_kernel<T>, dim3((unsigned)num_tokens), dim3(256), 0, (cudaStream_t)stream, 1, 
         (T*)query, (T*)key, positions, (const T*)cos_sin_cache, num_q_heads, num_kv_heads, head_size, rot_dim,
         q_stride_tok, k_stride_tok);
     B200_CHECK_LAUNCH();

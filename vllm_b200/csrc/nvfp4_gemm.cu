@@ -98,6 +98,8 @@ __global__ void __launch_bounds__(kF4Threads, 1)
   __syncthreads();
   umma::fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();
+  pdl_wait();  // setup above overlapped the previous kernel's tail
 
   if (warp == 0) {
     if (umma::elect_one()) {
@@ -232,7 +234,7 @@ static int launch_f4(const CUtensorMap& tx, const CUtensorMap& ty, const F4Args&
     }
     attr = true;
   }
-  kern<<<grid, kF4Threads, Cfg::SMEM_BYTES, stream>>>(tx, ty, g);
+  launch_kernel(kern, dim3(grid), dim3(kF4Threads), Cfg::SMEM_BYTES, stream, 1, tx, ty, g);
   B200_CHECK_LAUNCH();
   count_launch();
   return 0;

@@ -44,6 +44,8 @@ __global__ void __launch_bounds__(256) nvfp4_quant_kernel(uint32_t* __restrict__
                                                           const T* __restrict__ in,
                                                           const float* __restrict__ global_scale, int m, int n,
                                                           int out_n, int rows_total, int vecs_total) {
+  pdl_trigger();  // let the next kernel's prologue start
+  pdl_wait();     // predecessors' writes are visible from here on
   // rows_total / vecs_total include the padding the swizzled layout must zero.
   const float gs = global_scale ? global_scale[0] : 1.0f;
   const float rcp6 = rcp_approx_ftz(6.0f);
@@ -114,7 +116,7 @@ extern "C" int b200_scaled_fp4_quant(void* output, void* output_sf, const void* 
   dim3 grid(gx, gy), block(threads);
   cudaStream_t s = (cudaStream_t)stream;
 #define B200_Q4(T, SW)                                                                                             \
-  nvfp4_quant_kernel<T, SW><<<grid, block, 0, s>>>((uint32_t*)output, (uint8_t*)output_sf, (const T*)input,        \
+  launch_kernel(nvfp4_quant_kernel<T, SW>, dim3(grid), dim3(block), 0, s, 1, (uint32_t*)output, (uint8_t*)output_sf, (const T*)input,        \
                                                    input_global_scale, m, n, out_n, rows_total, vecs_total)
   if (dtype == B200_DT_BF16) {
     if (swizzled) B200_Q4(__nv_bfloat16, true);

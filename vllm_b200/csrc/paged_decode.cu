@@ -123,6 +123,9 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
   constexpr int SUB = Cfg::SUB_BYTES;
   constexpr int KS = D / 16;  // k-steps of QK^T == 16-wide d groups of PV
 
+  pdl_trigger();
+  pdl_wait();  // query, caches and seq_lens come from earlier kernels
+
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
   constexpr int kDataBytes = Cfg::RING_BYTES > Cfg::EPI_BYTES ? Cfg::RING_BYTES : Cfg::EPI_BYTES;
@@ -463,6 +466,8 @@ __global__ void __launch_bounds__(128) paged_decode_combine_kernel(
     QT* __restrict__ out, float* __restrict__ out_lse, const float* __restrict__ part_o,
     const float2* __restrict__ part_ml, const float* __restrict__ v_scale, int num_q_heads, int num_splits, int D,
     int64_t out_stride_seq, int64_t out_stride_head) {
+  pdl_trigger();
+  pdl_wait();
   const int h = blockIdx.x, seq = blockIdx.y;
   const int64_t base = ((int64_t)seq * num_q_heads + h) * num_splits;
   float mt = -INFINITY;
@@ -545,12 +550,12 @@ static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const Dec
     attr_set = true;
   }
   dim3 grid(a.num_splits, a.num_kv_heads * a.qgroups, num_seqs);
-  kern<<<grid, kWarps * 32, Cfg::SMEM_BYTES, stream>>>(tk, tv, a);
+  launch_kernel(kern, dim3(grid), dim3(kWarps * 32), Cfg::SMEM_BYTES, stream, 1, tk, tv, a);
   B200_CHECK_LAUNCH();
   count_launch();
   if (a.num_splits > 1) {
     dim3 g2(a.num_q_heads, num_seqs);
-    paged_decode_combine_kernel<QT><<<g2, 128, 0, stream>>>(
+    launch_kernel(paged_decode_combine_kernel<QT>, dim3(g2), dim3(128), 0, stream, 1, 
         reinterpret_cast<QT*>(a.out), a.out_lse, a.part_o, a.part_ml, KV == B200_KV_AUTO ? nullptr : a.v_scale,
         a.num_q_heads, a.num_splits, D, a.out_stride_seq, a.out_stride_head);
     B200_CHECK_LAUNCH();

@@ -4,6 +4,7 @@
 #include <cuda.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -23,6 +24,19 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+static std::atomic<int> g_pdl{-1};
+bool pdl_enabled() {
+  int v = g_pdl.load(std::memory_order_relaxed);
+  if (v < 0) {
+    const char* e = getenv("B200_PDL");  // default on; B200_PDL=0 restores plain stream order
+    v = (e && *e) ? (atoi(e) != 0) : 1;
+    g_pdl.store(v, std::memory_order_relaxed);
+  }
+  return v != 0;
+}
+void set_pdl(int on);
+void set_pdl(int on) { g_pdl.store(on ? 1 : 0, std::memory_order_relaxed); }
 
 int sm_count() {
   static int cached[64] = {0};
@@ -103,4 +117,6 @@ extern "C" {
 const char* b200_version(void) { return "b200vllm 1 sm_100a"; }
 const char* b200_last_error(void) { return b200::g_err; }
 int b200_num_kernels_launched(void) { return b200::g_launches.load(std::memory_order_relaxed); }
+void b200_set_pdl(int enabled) { b200::set_pdl(enabled); }
+int b200_get_pdl(void) { return b200::pdl_enabled() ? 1 : 0; }
 }

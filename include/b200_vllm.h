@@ -337,6 +337,9 @@ int b200_get_pdl(void);
  * phase boundaries (scripts/prof_gemm.py --trace).  Pass NULL to switch it off.
  * ---------------------------------------------------------------------- */
 void b200_debug_gemm_trace(unsigned long long* device_buffer);
+/* Same for the fp8 paged-attention kernel: [cta][32] stamps of one steady-state tile and per-barrier wait
+ * cycles (scripts/prof_attn.py). */
+void b200_debug_attn_trace(unsigned long long* device_buffer);
 /* Force the decode-regime work partition (tests / tuning): 0 whole tiles, 1 stream-K and 2 split-K
  * through the workspace, 3 cluster split-K over distributed shared memory, -1 automatic. */
 void b200_debug_gemm_mode(int mode);

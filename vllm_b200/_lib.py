@@ -69,6 +69,7 @@ SIGNATURES: dict[str, tuple] = {
     "b200_set_pdl": (None, [i32]),
     "b200_get_pdl": (i32, []),
     "b200_debug_gemm_trace": (None, [vp]),
+    "b200_debug_attn_trace": (None, [vp]),
     "b200_debug_gemm_mode": (None, [i32]),
 }
 

@@ -24,6 +24,7 @@ SOURCES = [
     "runtime.cu",
     "cache_write.cu",
     "paged_decode.cu",
+    "paged_decode_fp8.cu",
     "fp8_quant.cu",
     "nvfp4_quant.cu",
     "merge_elementwise.cu",

@@ -217,6 +217,17 @@ __device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4],
   }
 }
 
+// four floats -> four e4m3 bytes (x0 in the low byte), round-to-nearest, saturating
+__device__ __forceinline__ uint32_t pack4_e4m3(float x0, float x1, float x2, float x3) {
+  const uint32_t lo = __nv_cvt_float2_to_fp8x2(make_float2(x0, x1), __NV_SATFINITE, __NV_E4M3);
+  const uint32_t hi = __nv_cvt_float2_to_fp8x2(make_float2(x2, x3), __NV_SATFINITE, __NV_E4M3);
+  return lo | (hi << 16);
+}
+__device__ __forceinline__ float e4m3_to_float(uint32_t byte) {
+  const __half_raw h = __nv_cvt_fp8_to_halfraw((__nv_fp8_storage_t)byte, __NV_E4M3);
+  return __half2float(*reinterpret_cast<const __half*>(&h));
+}
+
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));

@@ -22,17 +22,13 @@
 //    second tiny kernel.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
-#include "common.cuh"
+#include "paged_decode.cuh"
 
 namespace b200 {
-
-constexpr int kChunk = 16;  // tokens per TMA box (block_size must be a multiple)
-constexpr int kWarps = 4;   // consumer warps per CTA
-constexpr float kLog2e = 1.4426950408889634f;
-constexpr float kLn2 = 0.6931471805599453f;
 
 template <int D, int KV> struct DecodeCfg {
   static constexpr int ES = (KV == B200_KV_AUTO) ? 2 : 1;  // bytes per cache element
@@ -49,23 +45,6 @@ template <int D, int KV> struct DecodeCfg {
   static constexpr int BAR_BYTES = kWarps * NSLOT * 8;
   static constexpr int SMEM_BYTES = (RING_BYTES > EPI_BYTES ? RING_BYTES : EPI_BYTES) + BAR_BYTES + 1024;
   static constexpr int BOX_D = 128 / ES;  // elements per 128-byte span
-};
-
-struct DecodeArgs {
-  void* out;
-  const void* query;
-  const int32_t* block_table;
-  const int32_t* seq_lens;
-  const float* k_scale;
-  const float* v_scale;
-  float* out_lse;
-  const int32_t* token_to_seq;  // optional: block_table row per query token
-  float* part_o;   // [seq][hq][split][D]
-  float2* part_ml; // [seq][hq][split]
-  int64_t q_stride_seq, q_stride_head, out_stride_seq, out_stride_head, block_table_stride;
-  int num_q_heads, num_kv_heads, group, qgroups;  // group = Hq/Hkv, qgroups = ceil(group/16)
-  int block_size, num_splits, sliding_window;
-  float scale, soft_cap;
 };
 
 __device__ __forceinline__ uint32_t pack2(float a, float b, __nv_bfloat16) {
@@ -86,12 +65,6 @@ template <int KV> __device__ __forceinline__ uint32_t fp8x2_to_h2(uint32_t x) {
   }
   return r;
 }
-__device__ __forceinline__ float fast_tanh(float x) {
-  float y;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
 template <typename QT> __device__ __forceinline__ uint32_t load_q_pair_as_half(const QT* p) {
   // fp8-KV path runs the MMAs in f16 (e4m3/e5m2 are exactly representable);
   // bf16 queries are converted with saturation to the f16 range.
@@ -549,10 +522,22 @@ static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const Dec
     }
     attr_set = true;
   }
-  dim3 grid(a.num_splits, a.num_kv_heads * a.qgroups, num_seqs);
-  launch_kernel(kern, dim3(grid), dim3(kWarps * 32), Cfg::SMEM_BYTES, stream, 1, tk, tv, a);
-  B200_CHECK_LAUNCH();
-  count_launch();
+  static const bool legacy_fp8 = [] {
+    const char* e = getenv("B200_ATTN_FP8_LEGACY");  // comparison aid: fp8 caches on the mma.sync kernel
+    return e && *e && atoi(e) != 0;
+  }();
+  if (KV != B200_KV_AUTO && !legacy_fp8) {
+    // fp8 caches run on tcgen05 (paged_decode_fp8.cu)
+    if constexpr (KV != B200_KV_AUTO && D != 64) {
+      int rc = launch_decode_fp8<QT, D, KV>(tk, tv, a, num_seqs, stream);
+      if (rc) return rc;
+    }
+  } else {
+    dim3 grid(a.num_splits, a.num_kv_heads * a.qgroups, num_seqs);
+    launch_kernel(kern, dim3(grid), dim3(kWarps * 32), Cfg::SMEM_BYTES, stream, 1, tk, tv, a);
+    B200_CHECK_LAUNCH();
+    count_launch();
+  }
   if (a.num_splits > 1) {
     dim3 g2(a.num_q_heads, num_seqs);
     launch_kernel(paged_decode_combine_kernel<QT>, dim3(g2), dim3(128), 0, stream, 1, 

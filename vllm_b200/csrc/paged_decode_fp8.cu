@@ -84,7 +84,11 @@ template <int D> struct Fp8Cfg {
   // K and V have separate rings: a K tile is released as soon as QK^T of its tile has run, a V tile only
   // after the softmax and PV - coupling them would hold K for the whole chain (measured: the ring, not the
   // softmax, bounds the kernel: throughput = ring bytes / (load latency + hold time)).
-  static constexpr int KST = 3, VST = 3;
+#ifndef B200_ATTN_KST
+#define B200_ATTN_KST 3
+#define B200_ATTN_VST 3
+#endif
+  static constexpr int KST = B200_ATTN_KST, VST = B200_ATTN_VST;
   static constexpr int RING_BYTES = (KST + VST) * OP_BYTES;
   static constexpr int Q_BYTES = 2 * NSUB * 16 * 128;  // Q hi, Q lo: [16 heads][D bytes] per span
   static constexpr int P_BYTES = 2 * 2 * 16 * 128;     // two buffers x (hi, lo) x [16 heads][128 tokens]
@@ -304,12 +308,28 @@ __global__ void __launch_bounds__(kF8Threads, (Fp8Cfg<D>::SMEM_BYTES <= 113 * 10
         a.block_table + (int64_t)(a.token_to_seq ? a.token_to_seq[seq] : seq) * a.block_table_stride;
     int stage = 0;
     uint32_t phase = 0;
-    WaitClock w_empty;
+    WaitClock w_empty, w_issue, w_loop;
+    const long long tp0 = clock64();
+    // Block ids are fetched 4 tiles (32 pieces, one per lane) at a time and one batch ahead: a dependent
+    // global load per tile in this loop caps the producer at ~1 tile/us (measured), below the HBM rate.
+    auto load_ids = [&](int batch) -> int {
+      const int pc = batch * 32 + lane, tile = pc >> 3;
+      if (tile < n_tiles) {
+        const int tok = (c0 + tile) * kTile + (pc & 7) * kChunk;
+        if (tok < len) return bt_row[tok / a.block_size];
+      }
+      return 0;
+    };
+    int ids_cur = load_ids(0), ids_next = load_ids(1);
     for (int i = 0; i < n_tiles; ++i) {
+      if ((i & 3) == 0 && i > 0) {
+        ids_cur = ids_next;
+        ids_next = load_ids((i >> 2) + 1);
+      }
       const int tok0 = (c0 + i) * kTile;
       const int my_tok = tok0 + lane * kChunk;
       const bool mine = lane < kTile / kChunk && my_tok < len;  // pieces that start past the sequence are not loaded
-      const int blk = mine ? bt_row[my_tok / a.block_size] : 0;
+      const int blk = __shfl_sync(0xffffffffu, ids_cur, (i & 3) * 8 + (lane & 7));
       const int n_valid = min(kTile / kChunk, (len - tok0 + kChunk - 1) / kChunk);
       if (lane == 0) {
         w_empty.wait(&emptyb[stage], phase ^ 1);
@@ -317,6 +337,7 @@ __global__ void __launch_bounds__(kF8Threads, (Fp8Cfg<D>::SMEM_BYTES <= 113 * 10
         mbar_arrive_expect_tx(&fullb[stage], (uint32_t)n_valid * NSUB * (kChunk * 128));
       }
       __syncwarp();
+      const long long ti0 = clock64();
       if (mine) {
         uint8_t* dst = ringb + stage * Cfg::OP_BYTES + lane * (kChunk * 128);
         const int tok_in_blk = my_tok % a.block_size;
@@ -324,12 +345,21 @@ __global__ void __launch_bounds__(kF8Threads, (Fp8Cfg<D>::SMEM_BYTES <= 113 * 10
         for (int sb = 0; sb < NSUB; ++sb)
           tma_load_4d(dst + sb * Cfg::SUB_TILE, tm, &fullb[stage], sb * 128, kvh, tok_in_blk, blk, kEvictFirst);
       }
+      __syncwarp();
+      w_issue.acc += clock64() - ti0;
       if (++stage == nst) {
         stage = 0;
         phase ^= 1;
       }
     }
-    if (lane == 0) w_empty.flush(is_k ? TW_K_EMPTY : TW_V_EMPTY);
+    if (lane == 0) {
+      w_empty.flush(is_k ? TW_K_EMPTY : TW_V_EMPTY);
+      if (is_k) {
+        w_issue.flush(27);
+        w_loop.acc = clock64() - tp0;
+        w_loop.flush(28);
+      }
+    }
   } else if (warp == 1) {
     // ===== QK^T issuer =====
     if (umma::elect_one()) {
@@ -461,6 +491,12 @@ __global__ void __launch_bounds__(kF8Threads, (Fp8Cfg<D>::SMEM_BYTES <= 113 * 10
       __syncwarp();
       if (lane == 0) mbar_arrive(&s_empty[b]);  // S buffer may be overwritten by QK^T of tile i+2
       if (trc) attn_stamp(TA_S_LOADED);
+#ifdef B200_ATTN_EXP_NOSOFTMAX  // timing experiment only (wrong results): no softmax work between QK^T and PV
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&p_full[b]);
+      if (i >= 2) fold_o(i - 2);
+      continue;
+#endif
 
       if (tok0 + kTile > len) {
         // boundary tile: V rows past the sequence were never loaded (or hold stale bytes); p is 0 there but

@@ -340,6 +340,9 @@ void b200_debug_gemm_trace(unsigned long long* device_buffer);
 /* Same for the fp8 paged-attention kernel: [cta][32] stamps of one steady-state tile and per-barrier wait
  * cycles (scripts/prof_attn.py). */
 void b200_debug_attn_trace(unsigned long long* device_buffer);
+/* fp8-cache decode kernel selection (tests / tuning): 1 = tcgen05 kernel, 0 = register-level kernel,
+ * -1 = default (register-level unless B200_ATTN_FP8_TCGEN05=1). */
+void b200_debug_attn_fp8_tcgen05(int mode);
 /* Force the decode-regime work partition (tests / tuning): 0 whole tiles, 1 stream-K and 2 split-K
  * through the workspace, 3 cluster split-K over distributed shared memory, -1 automatic. */
 void b200_debug_gemm_mode(int mode);

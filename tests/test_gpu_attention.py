@@ -192,6 +192,35 @@ def test_decode_fp8_kv(ops, kv, dtype, heads, D):
         torch.testing.assert_close(out, ref, atol=ATOL, rtol=RTOL)
 
 
+@pytest.mark.parametrize("kv", ["fp8", "fp8_e5m2"])
+@pytest.mark.parametrize("heads", [(32, 8), (8, 1), (16, 1)])
+def test_decode_fp8_kv_tcgen05_kernel(ops, kv, heads):
+    """The opt-in tcgen05 fp8 kernel (K/V tiles consumed from shared memory by UMMA) against the oracle:
+    contexts long enough to wrap its K/V rings and S/P/O double buffers several times, ragged tails, a
+    sliding window and both split settings."""
+    from vllm_b200 import _lib
+
+    Hq, Hkv = heads
+    bs, lens, D = 16, [2049, 130, 1, 1500, 128, 4000], 128
+    q, kc16, vc16, bt, sl, scale = _rand_case(21, len(lens), Hq, Hkv, D, bs, lens, torch.bfloat16)
+    ks, vs = torch.tensor([0.02]), torch.tensor([0.015])
+    kind = O.fp8_kind(kv)
+    kc = O.to_fp8(kc16.float() / ks, kind).view(torch.uint8)
+    vc = O.to_fp8(vc16.float() / vs, kind).view(torch.uint8)
+    ref = O.paged_attention_decode(q, kc, vc, bt, sl, scale, kv, float(ks), float(vs))
+    lib = _lib.load()
+    lib.b200_debug_attn_fp8_tcgen05(1)
+    try:
+        for splits in (1, 4):
+            out, _ = _run_decode(ops, q, kc, vc, bt, sl, scale, kv, ks, vs, splits=splits)
+            torch.testing.assert_close(out, ref, atol=ATOL, rtol=RTOL)
+            again, _ = _run_decode(ops, q, kc, vc, bt, sl, scale, kv, ks, vs, splits=splits)
+            assert torch.equal(out, again)
+        torch.cuda.synchronize()
+    finally:
+        lib.b200_debug_attn_fp8_tcgen05(-1)
+
+
 def test_decode_edge_cases(ops):
     # empty sequence -> zeros; stale block-table entries past the sequence must never be dereferenced;
     # NaN garbage in the unused tail of the last page must not leak

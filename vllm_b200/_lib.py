@@ -70,6 +70,7 @@ SIGNATURES: dict[str, tuple] = {
     "b200_get_pdl": (i32, []),
     "b200_debug_gemm_trace": (None, [vp]),
     "b200_debug_attn_trace": (None, [vp]),
+    "b200_debug_attn_fp8_tcgen05": (None, [i32]),
     "b200_debug_gemm_mode": (None, [i32]),
 }
 

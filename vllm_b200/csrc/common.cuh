@@ -142,8 +142,8 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
     if (++spins > (1u << 22)) {
-      printf("b200: mbarrier wait timed out (block %d,%d,%d thread %d parity %u)\n", blockIdx.x, blockIdx.y,
-             blockIdx.z, threadIdx.x, parity);
+      printf("b200: mbarrier wait timed out (block %d,%d,%d thread %d parity %u, barrier at shared 0x%x)\n", blockIdx.x,
+             blockIdx.y, blockIdx.z, threadIdx.x, parity, smem_u32(bar));
       __trap();
     }
   }

@@ -508,6 +508,8 @@ static int get_cache_tmap(CUtensorMap* out, const void* base, int D, int H, int 
   return 0;
 }
 
+static int g_fp8_tcgen05 = -1;  // b200_debug_attn_fp8_tcgen05: -1 environment, 0 register kernel, 1 tcgen05 kernel
+
 template <typename QT, int D, int KV>
 static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeArgs& a, int num_seqs,
                          cudaStream_t stream) {
@@ -522,10 +524,15 @@ static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const Dec
     }
     attr_set = true;
   }
-  static const bool legacy_fp8 = [] {
-    const char* e = getenv("B200_ATTN_FP8_LEGACY");  // comparison aid: fp8 caches on the mma.sync kernel
-    return e && *e && atoi(e) != 0;
+  // fp8 caches: the register-level kernel below is the default.  The tcgen05 kernel (paged_decode_fp8.cu)
+  // is parity-green but measured 5-15% slower on the BASELINE shapes (profiles/r01_attn_fp8_tcgen05.md:
+  // bound by the TMA request rate for 128-byte cache rows and by the QK->softmax->PV latency chain);
+  // B200_ATTN_FP8_TCGEN05=1 selects it.
+  static const bool env_legacy = [] {
+    const char* e = getenv("B200_ATTN_FP8_TCGEN05");
+    return !(e && *e && atoi(e) != 0);
   }();
+  const bool legacy_fp8 = g_fp8_tcgen05 >= 0 ? (g_fp8_tcgen05 == 0) : env_legacy;
   if (KV != B200_KV_AUTO && !legacy_fp8) {
     // fp8 caches run on tcgen05 (paged_decode_fp8.cu)
     if constexpr (KV != B200_KV_AUTO && D != 64) {
@@ -550,6 +557,8 @@ static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const Dec
 }
 
 }  // namespace b200
+
+extern "C" void b200_debug_attn_fp8_tcgen05(int mode) { b200::g_fp8_tcgen05 = mode; }
 
 extern "C" size_t b200_paged_decode_workspace_bytes(int num_seqs, int num_q_heads, int head_size, int num_splits) {
   if (num_splits <= 1) return 0;
@@ -636,6 +645,8 @@ extern "C" int b200_paged_attention_decode(const b200_paged_decode_params* p, b2
     splits = b200_paged_decode_pick_splits(p->num_seqs, p->num_kv_heads * a.qgroups,
                                            p->max_seq_len > 0 ? p->max_seq_len : 1, sm_count());
   a.num_splits = splits;
+  a.eff_splits = splits;
+  a.max_seq_len = p->max_seq_len;
   a.part_o = nullptr;
   a.part_ml = nullptr;
   if (splits > 1) {

@@ -27,6 +27,8 @@ struct DecodeArgs {
   int num_q_heads, num_kv_heads, group, qgroups;  // group = Hq/Hkv, qgroups = ceil(group/16)
   int block_size, num_splits, sliding_window;
   float scale, soft_cap;
+  int max_seq_len;  // upper bound from the caller (<= 0: unknown)
+  int eff_splits;   // fp8 kernel: splits that actually get work (<= num_splits; the others write empty partials)
 };
 
 __device__ __forceinline__ float fast_tanh(float x) {

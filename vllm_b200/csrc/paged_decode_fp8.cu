@@ -32,6 +32,8 @@
 //               groups keep independent (m, l, O) states, merged once at the end like split-KV partials.
 #include <cuda.h>
 
+#include <cstdlib>
+
 #include "paged_decode.cuh"
 #include "umma.cuh"
 
@@ -172,7 +174,7 @@ __global__ void __launch_bounds__(kF8Threads, (Fp8Cfg<D>::SMEM_BYTES <= 113 * 10
   const int lo = (a.sliding_window > 0) ? max(0, len - a.sliding_window) : 0;
   const int c_begin = lo / kTile, c_end = (len + kTile - 1) / kTile;
   const int nc = max(0, c_end - c_begin);
-  const int cps = (nc + a.num_splits - 1) / a.num_splits;
+  const int cps = (nc + a.eff_splits - 1) / a.eff_splits;
   const int c0 = c_begin + split * cps;
   const int c1 = min(c_end, c0 + cps);
   const int n_tiles = c1 - c0;
@@ -544,6 +546,10 @@ __global__ void __launch_bounds__(kF8Threads, (Fp8Cfg<D>::SMEM_BYTES <= 113 * 10
         l_thr[h] = l_thr[h] * al[h] + p;
         v[h] = p;
       }
+      // Fold this group's previous tile first: waiting for its O^T also guarantees that PV(i-2) has finished
+      // reading P^T buffer b, which is overwritten next, and keeps p_full from lapping its consumer (a
+      // barrier that completes two phases ahead of a waiter deadlocks it).
+      if (i >= 2) fold_o(i - 2);
       // p * 2^8 = hi + lo: hi = p truncated to 3 mantissa bits (exactly an e4m3), lo rounded to e4m3
       {
         uint8_t* ph = p_tiles + b * 4096;
@@ -565,8 +571,6 @@ __global__ void __launch_bounds__(kF8Threads, (Fp8Cfg<D>::SMEM_BYTES <= 113 * 10
       __syncwarp();
       if (lane == 0) mbar_arrive(&p_full[b]);
       if (trc) attn_stamp(TA_P_READY);
-
-      if (i >= 2) fold_o(i - 2);
 #pragma unroll
       for (int h = 0; h < NH; ++h) alpha_prev[h] = al[h];
     }
@@ -668,8 +672,34 @@ static int launch_fp8_nh(const CUtensorMap& tk, const CUtensorMap& tv, const Dec
 }
 
 template <typename QT, int D, int KV>
-int launch_decode_fp8(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeArgs& a, int num_seqs,
+int launch_decode_fp8(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeArgs& a_in, int num_seqs,
                       cudaStream_t stream) {
+  // Fewer, longer CTAs than the caller's split count when that pays: a CTA spends ~2 tile-times in its
+  // prologue/merge, and the grid should still fill the 2-per-SM slots evenly.  Splits >= eff exit at once
+  // with empty partials, so the caller's workspace layout and combine stay valid.
+  DecodeArgs a = a_in;
+  {
+    static const int force = [] {
+      const char* e = getenv("B200_ATTN_FP8_SPLITS");
+      return (e && *e) ? atoi(e) : 0;
+    }();
+    const long base = (long)num_seqs * a.num_kv_heads * a.qgroups;
+    const long slots = 2L * sm_count();
+    const int total_tiles = a.max_seq_len > 0 ? (a.max_seq_len + kTile - 1) / kTile : 32 * a.num_splits;
+    int best = 1;
+    double best_eff = 0.0;
+    for (int s = 1; s <= a.num_splits; ++s) {
+      const double waves = (double)(base * s) / slots;
+      const double fill = waves / (double)((long)(waves + 0.999999));
+      const double per = (double)((total_tiles + s - 1) / s);  // tiles per CTA
+      const double eff = fill * per / (per + 2.0);
+      if (eff > best_eff * 1.02) {
+        best_eff = eff;
+        best = s;
+      }
+    }
+    a.eff_splits = (force > 0 && force <= a.num_splits) ? force : best;
+  }
   const int live = a.group < 16 ? a.group : 16;  // heads per CTA
   if (live <= 4) return launch_fp8_nh<QT, D, KV, 4>(tk, tv, a, num_seqs, stream);
   if (live <= 8) return launch_fp8_nh<QT, D, KV, 8>(tk, tv, a, num_seqs, stream);

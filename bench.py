@@ -162,17 +162,24 @@ def run_ours(args) -> None:
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     _lib.load()
+
+    def stage(msg: str) -> None:  # progress on stderr (stdout carries exactly one JSON line)
+        if world > 1 or os.environ.get("B200_BENCH_VERBOSE"):
+            print(f"[bench rank {rank}/{world}] {msg}", file=sys.stderr, flush=True)
+
     group = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
+        stage("process group up")
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
 
     B, ctx = args.batch, args.ctx
     runner = DecodeRunner(LLAMA_8B, B, ctx, kv_cache_dtype="fp8", weight_quant="fp8", tp_size=world, tp_rank=rank,
                           device=dev, tp_group=group, num_layers=args.layers)
     runner.set_batch(ctx)
+    stage("runner built")
     if args.profile_step:
         # for `ncu --profile-from-start off`: exactly one eager step between profiler start/stop
         runner.step_eager()
@@ -185,6 +192,7 @@ def run_ours(args) -> None:
         print(json.dumps({"profile_step": True, "launches_ours": _lib.num_kernels_launched()}))
         return
     runner.capture(warmup=2)
+    stage("step captured")
 
     def barrier():
         if world > 1:
@@ -212,6 +220,7 @@ def run_ours(args) -> None:
     e1.record()
     barrier()
     ms_dev = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    stage(f"device-resident timing done: {ms_dev:.3f} ms/step")
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- end to end: pinned host inputs -> H2D -> step -> D2H of the sampled tokens, every step
@@ -302,7 +311,17 @@ def run_ours(args) -> None:
                                         "sample": f"failed: {e!r}"}
         print(json.dumps(line))
     if world > 1:
-        dist.destroy_process_group()
+        # Tear-down: a captured graph that holds NCCL kernels makes ncclCommDestroy block (observed: the JSON line
+        # printed, then both ranks hung in destroy_process_group until the launcher's timeout).  Release the
+        # graph, drain the device, agree that every rank is done, and leave without the communicator teardown.
+        sys.stdout.flush()
+        runner.graph = None
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=group)
+        torch.cuda.synchronize(dev)
+        stage("done")
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main() -> None:

@@ -32,7 +32,10 @@ template <int BN> struct GemmCfg {
   static constexpr int X_BYTES = 128 * kBK;
   static constexpr int Y_BYTES = BN * kBK;
   static constexpr int STAGE_BYTES = X_BYTES + Y_BYTES;
-  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+#ifndef B200_GEMM_SMEM_KB
+#define B200_GEMM_SMEM_KB 200
+#endif
+  static constexpr int STAGES = (B200_GEMM_SMEM_KB * 1024) / STAGE_BYTES > 8 ? 8 : (B200_GEMM_SMEM_KB * 1024) / STAGE_BYTES;
   static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
@@ -85,7 +88,7 @@ template <> __device__ __forceinline__ void store16<__half>(__half* dst, const f
 // X rows -> TMEM lanes (128 per CTA), Y rows -> TMEM columns (BN per CTA).
 // kSwap == false: X = A (tokens, M), Y = B (weights, N).  kSwap == true: X = B, Y = A.
 template <int BN, bool kSwap, typename OutT>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(kGemmThreads, B200_GEMM_SMEM_KB <= 110 ? 2 : 1)
     fp8_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_y,
                     const GemmArgs g) {
   using Cfg = GemmCfg<BN>;

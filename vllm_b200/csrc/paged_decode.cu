@@ -34,11 +34,17 @@ template <int D, int KV> struct DecodeCfg {
   static constexpr int ES = (KV == B200_KV_AUTO) ? 2 : 1;  // bytes per cache element
   static constexpr int ROWB = D * ES;                      // bytes per (token, head) row
   static_assert(ROWB % 128 == 0, "row must be a whole number of 128-byte swizzle spans");
-  static constexpr int NSUB = ROWB / 128;           // TMA boxes per K (or V) chunk
+  static constexpr int NSUB = ROWB / 128;           // TMA boxes per 16-token K (or V) piece
   static constexpr int SUB_BYTES = kChunk * 128;    // 2 KB, 1024-aligned
-  static constexpr int KCH_BYTES = NSUB * SUB_BYTES;
-  static constexpr int SLOT_BYTES = 2 * KCH_BYTES;  // K chunk + V chunk
-  static constexpr int NSLOT = ROWB >= 512 ? 2 : (ROWB == 256 ? 3 : 4);
+  // fp8 caches: a ring slot holds 32 tokens (two 16-token pieces).  The kernel is issue-bound there (64 converts
+  // per 16 tokens) and ~150 of its ~450 instructions per 16 tokens were per-slot overhead (barrier wait, TMA
+  // issue, masks, max/rescale bookkeeping) - twice the tokens per slot halves that share.
+  static constexpr int TOK = (KV == B200_KV_AUTO) ? 16 : 32;
+  static constexpr int NBOX = TOK / kChunk;
+  static constexpr int BOX_BYTES = NSUB * SUB_BYTES;  // one 16-token piece of K (or V)
+  static constexpr int KCH_BYTES = NBOX * BOX_BYTES;
+  static constexpr int SLOT_BYTES = 2 * KCH_BYTES;  // K part + V part
+  static constexpr int NSLOT = (KV != B200_KV_AUTO) ? 2 : (ROWB >= 512 ? 2 : (ROWB == 256 ? 3 : 4));
   static constexpr int RING_BYTES = kWarps * NSLOT * SLOT_BYTES;
   static constexpr int OPAD = D + 8;  // fp32 row pitch of the merge buffer
   static constexpr int EPI_BYTES = kWarps * 16 * OPAD * 4 + 2 * kWarps * 16 * 4;
@@ -84,7 +90,9 @@ template <int SMEM> struct OccFor {
   static constexpr int value = SMEM <= 74 * 1024 ? 3 : (SMEM <= 112 * 1024 ? 2 : 1);
 };
 
-template <typename QT, int D, int KV>
+// R8: every CTA has at most 8 live query heads (GQA group <= 8): rows g+8 of the MMA tiles are padding and
+// their share of the softmax is skipped.
+template <typename QT, int D, int KV, bool R8>
 __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYTES>::value)
     paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k, const __grid_constant__ CUtensorMap tmap_v,
                         const DecodeArgs a) {
@@ -95,6 +103,7 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
   constexpr int NSLOT = Cfg::NSLOT;
   constexpr int SUB = Cfg::SUB_BYTES;
   constexpr int KS = D / 16;  // k-steps of QK^T == 16-wide d groups of PV
+  constexpr int TOK = Cfg::TOK, NBOX = Cfg::NBOX, NT = TOK / 8;
 
   pdl_trigger();
   pdl_wait();  // query, caches and seq_lens come from earlier kernels
@@ -111,7 +120,7 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
   const int qh0 = kvh * a.group + qg * 16;
   const int len = a.seq_lens[seq];
   const int lo = (a.sliding_window > 0) ? max(0, len - a.sliding_window) : 0;
-  const int c_begin = lo / kChunk, c_end = (len + kChunk - 1) / kChunk;
+  const int c_begin = lo / TOK, c_end = (len + TOK - 1) / TOK;
   const int nc = max(0, c_end - c_begin);
   int cps = (nc + a.num_splits - 1) / a.num_splits;
   cps = (cps + kWarps - 1) / kWarps * kWarps;
@@ -182,32 +191,55 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
   uint64_t* wbar = bars + warp * NSLOT;
   const int32_t* bt_row =
       a.block_table + (int64_t)(a.token_to_seq ? a.token_to_seq[seq] : seq) * a.block_table_stride;
-  auto load_ids = [&](int batch) -> int {
+  // block id of 16-token piece h of this lane's slot in `batch` (0 where the piece starts past the sequence:
+  // such a piece is not loaded, and the table may not extend that far)
+  auto load_id = [&](int batch, int h) -> int {
     const int i = batch * 32 + lane;
-    if (i < n_my) return bt_row[((c0 + warp + kWarps * i) * kChunk) / a.block_size];
+    if (i < n_my) {
+      const int tok = (c0 + warp + kWarps * i) * TOK + h * kChunk;
+      if (tok < len) return bt_row[tok / a.block_size];
+    }
     return 0;
   };
-  int ids_cur = load_ids(0), ids_next = load_ids(1), issue_batch = 0;
+  int ids_cur[NBOX], ids_next[NBOX], issue_batch = 0;
+#pragma unroll
+  for (int h = 0; h < NBOX; ++h) {
+    ids_cur[h] = load_id(0, h);
+    ids_next[h] = load_id(1, h);
+  }
   auto issue = [&](int ii, int slot) {
     const int b = ii >> 5;
     if (b != issue_batch) {
-      ids_cur = ids_next;
-      ids_next = load_ids(b + 1);
+#pragma unroll
+      for (int h = 0; h < NBOX; ++h) {
+        ids_cur[h] = ids_next[h];
+        ids_next[h] = load_id(b + 1, h);
+      }
       issue_batch = b;
     }
-    const int blk = __shfl_sync(0xffffffffu, ids_cur, ii & 31);
+    int blk[NBOX];
+#pragma unroll
+    for (int h = 0; h < NBOX; ++h) blk[h] = __shfl_sync(0xffffffffu, ids_cur[h], ii & 31);
     if (lane == 0) {
-      const int c = c0 + warp + kWarps * ii;
-      const int tok_in_blk = (c * kChunk) % a.block_size;
+      const int tok0 = (c0 + warp + kWarps * ii) * TOK;
       uint8_t* dst = ring + slot * Cfg::SLOT_BYTES;
-      mbar_arrive_expect_tx(&wbar[slot], Cfg::SLOT_BYTES);
+      int nload = 0;
 #pragma unroll
-      for (int s = 0; s < Cfg::NSUB; ++s)
-        tma_load_4d(dst + s * SUB, &tmap_k, &wbar[slot], s * Cfg::BOX_D, kvh, tok_in_blk, blk, kEvictFirst);
+      for (int h = 0; h < NBOX; ++h) nload += (tok0 + h * kChunk < len);
+      mbar_arrive_expect_tx(&wbar[slot], (uint32_t)nload * 2u * Cfg::BOX_BYTES);
 #pragma unroll
-      for (int s = 0; s < Cfg::NSUB; ++s)
-        tma_load_4d(dst + Cfg::KCH_BYTES + s * SUB, &tmap_v, &wbar[slot], s * Cfg::BOX_D, kvh, tok_in_blk, blk,
-                    kEvictFirst);
+      for (int h = 0; h < NBOX; ++h) {
+        if (tok0 + h * kChunk >= len) continue;
+        const int tok_in_blk = (tok0 + h * kChunk) % a.block_size;
+#pragma unroll
+        for (int sb = 0; sb < Cfg::NSUB; ++sb)
+          tma_load_4d(dst + h * Cfg::BOX_BYTES + sb * SUB, &tmap_k, &wbar[slot], sb * Cfg::BOX_D, kvh, tok_in_blk,
+                      blk[h], kEvictFirst);
+#pragma unroll
+        for (int sb = 0; sb < Cfg::NSUB; ++sb)
+          tma_load_4d(dst + Cfg::KCH_BYTES + h * Cfg::BOX_BYTES + sb * SUB, &tmap_v, &wbar[slot], sb * Cfg::BOX_D,
+                      kvh, tok_in_blk, blk[h], kEvictFirst);
+      }
     }
   };
   {
@@ -238,22 +270,25 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
     const uint32_t vbase = kbase + Cfg::KCH_BYTES;
     mbar_wait(&wbar[slot], phase);
 
-    const int tok0 = c * kChunk;
-    if (tok0 + kChunk > len) {
-      // boundary chunk: rows past seq_len may hold stale/garbage bytes; p is 0
-      // there but 0 * NaN would poison the accumulator, so clear V rows.
+    const int tok0 = c * TOK;
+    if (tok0 + TOK > len) {
+      // boundary slot: rows past seq_len hold stale / never-loaded bytes; p is 0 there but 0 * NaN would
+      // poison the accumulator, so clear those V rows (K garbage only reaches masked logits).
       const int valid = len - tok0;
       uint8_t* vs = ring + slot * Cfg::SLOT_BYTES + Cfg::KCH_BYTES;
-      for (int idx = lane; idx < (kChunk - valid) * Cfg::NSUB * 8; idx += 32) {
+      for (int idx = lane; idx < (TOK - valid) * Cfg::NSUB * 8; idx += 32) {
         const int row = valid + idx / (Cfg::NSUB * 8);
         const int rem = idx % (Cfg::NSUB * 8);
-        *reinterpret_cast<uint4*>(vs + (rem >> 3) * SUB + row * 128 + (rem & 7) * 16) = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(vs + (row >> 4) * Cfg::BOX_BYTES + (rem >> 3) * SUB + (row & 15) * 128 +
+                                  (rem & 7) * 16) = make_uint4(0, 0, 0, 0);
       }
       __syncwarp();
     }
 
     // ---- S = Q K^T (16 x 16 tokens) ---------------------------------------
-    float s[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+    float s[NT][4];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
     if constexpr (!kFp8) {
 #pragma unroll
       for (int ks = 0; ks < KS; ++ks) {
@@ -265,23 +300,27 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
       }
     } else {
 #pragma unroll
-      for (int jj = 0; jj < KS / 2; ++jj) {
-        const int dch = 2 * jj + k_cof;  // 16-byte column = one k-step of 16 fp8
-        uint32_t b[4];
-        ldmatrix_x4(b, kbase + (dch >> 3) * SUB + k_tok * 128 + (((dch & 7) ^ lr) << 4));
-        mma_16816<false>(s[0], qa[2 * jj], fp8x2_to_h2<KV>(b[0]), fp8x2_to_h2<KV>(b[0] >> 16));
-        mma_16816<false>(s[1], qa[2 * jj], fp8x2_to_h2<KV>(b[1]), fp8x2_to_h2<KV>(b[1] >> 16));
-        mma_16816<false>(s[0], qa[2 * jj + 1], fp8x2_to_h2<KV>(b[2]), fp8x2_to_h2<KV>(b[2] >> 16));
-        mma_16816<false>(s[1], qa[2 * jj + 1], fp8x2_to_h2<KV>(b[3]), fp8x2_to_h2<KV>(b[3] >> 16));
+      for (int hb = 0; hb < NBOX; ++hb) {  // 16-token pieces of the slot
+#pragma unroll
+        for (int jj = 0; jj < KS / 2; ++jj) {
+          const int dch = 2 * jj + k_cof;  // 16-byte column = one k-step of 16 fp8
+          uint32_t b[4];
+          ldmatrix_x4(b, kbase + hb * Cfg::BOX_BYTES + (dch >> 3) * SUB + k_tok * 128 + (((dch & 7) ^ lr) << 4));
+          mma_16816<false>(s[2 * hb], qa[2 * jj], fp8x2_to_h2<KV>(b[0]), fp8x2_to_h2<KV>(b[0] >> 16));
+          mma_16816<false>(s[2 * hb + 1], qa[2 * jj], fp8x2_to_h2<KV>(b[1]), fp8x2_to_h2<KV>(b[1] >> 16));
+          mma_16816<false>(s[2 * hb], qa[2 * jj + 1], fp8x2_to_h2<KV>(b[2]), fp8x2_to_h2<KV>(b[2] >> 16));
+          mma_16816<false>(s[2 * hb + 1], qa[2 * jj + 1], fp8x2_to_h2<KV>(b[3]), fp8x2_to_h2<KV>(b[3] >> 16));
+        }
       }
     }
 
     // ---- scale, soft-cap, mask ------------------------------------------------
-    const bool need_mask = (tok0 + kChunk > len) || (tok0 < lo);
+    const bool need_mask = (tok0 + TOK > len) || (tok0 < lo);
+    constexpr int NE = R8 ? 2 : 4;  // accumulator elements per n-tile that belong to live rows
 #pragma unroll
-    for (int nt = 0; nt < 2; ++nt)
+    for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
+      for (int e = 0; e < NE; ++e) {
         float v = use_cap ? cap_l2 * fast_tanh(s[nt][e] * sc_nat * cap_inv) : s[nt][e] * sc;
         if (need_mask) {
           const int tok = tok0 + nt * 8 + 2 * t + (e & 1);
@@ -289,44 +328,66 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
         }
         s[nt][e] = v;
       }
-    float mx0 = fmaxf(fmaxf(s[0][0], s[0][1]), fmaxf(s[1][0], s[1][1]));
-    float mx1 = fmaxf(fmaxf(s[0][2], s[0][3]), fmaxf(s[1][2], s[1][3]));
+    float mx0 = fmaxf(s[0][0], s[0][1]), mx1 = R8 ? 0.f : fmaxf(s[0][2], s[0][3]);
+#pragma unroll
+    for (int nt = 1; nt < NT; ++nt) {
+      mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
+      if constexpr (!R8) mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
+    }
     mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
     mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-    const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);
+    if constexpr (!R8) {
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    }
+    const float mn0 = fmaxf(m0, mx0), mn1 = R8 ? m1 : fmaxf(m1, mx1);
     const float ms0 = (mn0 == -INFINITY) ? 0.f : mn0, ms1 = (mn1 == -INFINITY) ? 0.f : mn1;
-    const float al0 = fast_exp2(m0 - ms0), al1 = fast_exp2(m1 - ms1);
+    const float al0 = fast_exp2(m0 - ms0), al1 = R8 ? 1.f : fast_exp2(m1 - ms1);
     m0 = mn0;
     m1 = mn1;
-    float p[2][4];
+    float p[NT][4];
+    float ps0 = 0.f, ps1 = 0.f;
 #pragma unroll
-    for (int nt = 0; nt < 2; ++nt) {
+    for (int nt = 0; nt < NT; ++nt) {
       p[nt][0] = fast_exp2(s[nt][0] - ms0);
       p[nt][1] = fast_exp2(s[nt][1] - ms0);
-      p[nt][2] = fast_exp2(s[nt][2] - ms1);
-      p[nt][3] = fast_exp2(s[nt][3] - ms1);
+      ps0 += p[nt][0] + p[nt][1];
+      if constexpr (R8) {
+        p[nt][2] = p[nt][3] = 0.f;
+      } else {
+        p[nt][2] = fast_exp2(s[nt][2] - ms1);
+        p[nt][3] = fast_exp2(s[nt][3] - ms1);
+        ps1 += p[nt][2] + p[nt][3];
+      }
     }
-    l0 = l0 * al0 + (p[0][0] + p[0][1] + p[1][0] + p[1][1]);
-    l1 = l1 * al1 + (p[0][2] + p[0][3] + p[1][2] + p[1][3]);
+    l0 = l0 * al0 + ps0;
+    if constexpr (!R8) l1 = l1 * al1 + ps1;
     if (__any_sync(0xffffffffu, (al0 != 1.f) || (al1 != 1.f))) {
 #pragma unroll
       for (int n = 0; n < 2 * KS; ++n) {
         o[n][0] *= al0;
         o[n][1] *= al0;
-        o[n][2] *= al1;
-        o[n][3] *= al1;
+        if constexpr (!R8) {
+          o[n][2] *= al1;
+          o[n][3] *= al1;
+        }
       }
     }
-    uint32_t pa[4];
-    pa[0] = pack2(p[0][0], p[0][1], MT());
-    pa[1] = pack2(p[0][2], p[0][3], MT());
-    pa[2] = pack2(p[1][0], p[1][1], MT());
-    pa[3] = pack2(p[1][2], p[1][3], MT());
 
     // ---- O += P V -----------------------------------------------------------
+    auto pack_p = [&](int hb, uint32_t (&pa)[4]) {  // A fragment of the 16 tokens of piece hb
+      pa[0] = pack2(p[2 * hb][0], p[2 * hb][1], MT());
+      pa[2] = pack2(p[2 * hb + 1][0], p[2 * hb + 1][1], MT());
+      if constexpr (R8) {
+        pa[1] = pa[3] = 0u;
+      } else {
+        pa[1] = pack2(p[2 * hb][2], p[2 * hb][3], MT());
+        pa[3] = pack2(p[2 * hb + 1][2], p[2 * hb + 1][3], MT());
+      }
+    };
     if constexpr (!kFp8) {
+      uint32_t pa[4];
+      pack_p(0, pa);
 #pragma unroll
       for (int j = 0; j < KS; ++j) {
         const int dch = 2 * j + v_cof;
@@ -340,19 +401,24 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
       // transpose a thread holds tokens (2t, 2t+1) x columns (2g, 2g+1); the even
       // / odd column of every pair feeds a separate n-tile (d = 16c + 2n + par).
 #pragma unroll
-      for (int jj = 0; jj < KS / 2; ++jj) {
-        const int dch = 2 * jj + v_cof;
-        uint32_t b[4];
-        ldmatrix_x4_trans(b, vbase + (dch >> 3) * SUB + v_tok * 128 + (((dch & 7) ^ lr) << 4));
+      for (int hb = 0; hb < NBOX; ++hb) {
+        uint32_t pa[4];
+        pack_p(hb, pa);
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {  // 16-byte column 2jj + h
-          const uint32_t lo_t = b[2 * h], hi_t = b[2 * h + 1];  // tokens 0-7 / 8-15
-          const uint32_t be0 = fp8x2_to_h2<KV>(__byte_perm(lo_t, 0, 0x0020));
-          const uint32_t be1 = fp8x2_to_h2<KV>(__byte_perm(hi_t, 0, 0x0020));
-          const uint32_t bo0 = fp8x2_to_h2<KV>(__byte_perm(lo_t, 0, 0x0031));
-          const uint32_t bo1 = fp8x2_to_h2<KV>(__byte_perm(hi_t, 0, 0x0031));
-          mma_16816<false>(o[2 * (2 * jj + h)], pa, be0, be1);
-          mma_16816<false>(o[2 * (2 * jj + h) + 1], pa, bo0, bo1);
+        for (int jj = 0; jj < KS / 2; ++jj) {
+          const int dch = 2 * jj + v_cof;
+          uint32_t b[4];
+          ldmatrix_x4_trans(b, vbase + hb * Cfg::BOX_BYTES + (dch >> 3) * SUB + v_tok * 128 + (((dch & 7) ^ lr) << 4));
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {  // 16-byte column 2jj + h
+            const uint32_t lo_t = b[2 * h], hi_t = b[2 * h + 1];  // tokens 0-7 / 8-15
+            const uint32_t be0 = fp8x2_to_h2<KV>(__byte_perm(lo_t, 0, 0x0020));
+            const uint32_t be1 = fp8x2_to_h2<KV>(__byte_perm(hi_t, 0, 0x0020));
+            const uint32_t bo0 = fp8x2_to_h2<KV>(__byte_perm(lo_t, 0, 0x0031));
+            const uint32_t bo1 = fp8x2_to_h2<KV>(__byte_perm(hi_t, 0, 0x0031));
+            mma_16816<false>(o[2 * (2 * jj + h)], pa, be0, be1);
+            mma_16816<false>(o[2 * (2 * jj + h) + 1], pa, bo0, bo1);
+          }
         }
       }
     }
@@ -514,15 +580,16 @@ template <typename QT, int D, int KV>
 static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeArgs& a, int num_seqs,
                          cudaStream_t stream) {
   using Cfg = DecodeCfg<D, KV>;
-  static bool attr_set = false;
-  auto kern = paged_decode_kernel<QT, D, KV>;
-  if (!attr_set) {
+  static bool attr_set[2] = {false, false};
+  const bool r8 = a.group <= 8;
+  auto kern = r8 ? paged_decode_kernel<QT, D, KV, true> : paged_decode_kernel<QT, D, KV, false>;
+  if (!attr_set[r8]) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
       return B200_ERR_CUDA;
     }
-    attr_set = true;
+    attr_set[r8] = true;
   }
   // fp8 caches: the register-level kernel below is the default.  The tcgen05 kernel (paged_decode_fp8.cu)
   // is parity-green but measured 5-15% slower on the BASELINE shapes (profiles/r01_attn_fp8_tcgen05.md:

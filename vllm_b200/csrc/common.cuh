@@ -199,6 +199,14 @@ __device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], uint32_t add
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
                : "r"(addr));
 }
+// two transposed 16x16 byte matrices: lane (g = lane/4, t = lane%4) receives source rows 4t..4t+3 at column g
+// (r0), at column g+8 (r1), and the same of the second matrix (r2, r3); lane L supplies the address of source
+// row L%16 of matrix L/16 (layout checked on the device by scripts/ldm_probe.cu).  sm_100a only.
+__device__ __forceinline__ void ldmatrix_b8_x2_trans(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m16n16.x2.trans.shared.b8 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
 // D(16x8,f32) += A(16x16) * B(16x8), bf16 or f16 operands.
 template <bool kBf16>
 __device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {

@@ -71,6 +71,18 @@ template <int KV> __device__ __forceinline__ uint32_t fp8x2_to_h2(uint32_t x) {
   }
   return r;
 }
+// four fp8 bytes -> f16x2 of bytes (0,1) and f16x2 of bytes (2,3); the halves are sub-registers, no shift
+template <int KV> __device__ __forceinline__ void fp8x4_to_h2x2(uint32_t x, uint32_t& lo, uint32_t& hi) {
+  if constexpr (KV == B200_KV_FP8_E5M2) {
+    asm("{\n\t.reg .b16 l, h;\n\tmov.b32 {l, h}, %2;\n\tcvt.rn.f16x2.e5m2x2 %0, l;\n\tcvt.rn.f16x2.e5m2x2 %1, h;\n\t}"
+        : "=r"(lo), "=r"(hi)
+        : "r"(x));
+  } else {
+    asm("{\n\t.reg .b16 l, h;\n\tmov.b32 {l, h}, %2;\n\tcvt.rn.f16x2.e4m3x2 %0, l;\n\tcvt.rn.f16x2.e4m3x2 %1, h;\n\t}"
+        : "=r"(lo), "=r"(hi)
+        : "r"(x));
+  }
+}
 template <typename QT> __device__ __forceinline__ uint32_t load_q_pair_as_half(const QT* p) {
   // fp8-KV path runs the MMAs in f16 (e4m3/e5m2 are exactly representable);
   // bf16 queries are converted with saturation to the f16 range.
@@ -257,7 +269,9 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
   const int li = lane >> 3, lr = lane & 7;
   // 16-bit KV:  K matrices (tok-lo,d-lo)(tok-lo,d-hi)(tok-hi,d-lo)(tok-hi,d-hi); V.trans (tok-lo,d)(tok-hi,d)(tok-lo,d+1)(tok-hi,d+1)
   // fp8 KV:     K and V both (tok-lo,c)(tok-hi,c)(tok-lo,c+1)(tok-hi,c+1) with c = 16-byte column
-  const int k_tok = kFp8 ? ((li & 1) << 3) + lr : ((li >> 1) << 3) + lr;
+  // fp8: S column c of n-tile nt holds token 4*(c/2) + 2*nt + (c&1), so that a thread's four S values of a
+  // 16-token piece are the tokens 4t..4t+3 - the order in which the transposed byte ldmatrix of V delivers them
+  const int k_tok = kFp8 ? 4 * (lr >> 1) + 2 * (li & 1) + (lr & 1) : ((li >> 1) << 3) + lr;
   const int k_cof = kFp8 ? (li >> 1) : (li & 1);
   const int v_tok = ((li & 1) << 3) + lr;
   const int v_cof = li >> 1;
@@ -305,11 +319,14 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
         for (int jj = 0; jj < KS / 2; ++jj) {
           const int dch = 2 * jj + k_cof;  // 16-byte column = one k-step of 16 fp8
           uint32_t b[4];
-          ldmatrix_x4(b, kbase + hb * Cfg::BOX_BYTES + (dch >> 3) * SUB + k_tok * 128 + (((dch & 7) ^ lr) << 4));
-          mma_16816<false>(s[2 * hb], qa[2 * jj], fp8x2_to_h2<KV>(b[0]), fp8x2_to_h2<KV>(b[0] >> 16));
-          mma_16816<false>(s[2 * hb + 1], qa[2 * jj], fp8x2_to_h2<KV>(b[1]), fp8x2_to_h2<KV>(b[1] >> 16));
-          mma_16816<false>(s[2 * hb], qa[2 * jj + 1], fp8x2_to_h2<KV>(b[2]), fp8x2_to_h2<KV>(b[2] >> 16));
-          mma_16816<false>(s[2 * hb + 1], qa[2 * jj + 1], fp8x2_to_h2<KV>(b[3]), fp8x2_to_h2<KV>(b[3] >> 16));
+          ldmatrix_x4(b, kbase + hb * Cfg::BOX_BYTES + (dch >> 3) * SUB + k_tok * 128 + (((dch & 7) ^ (k_tok & 7)) << 4));
+          uint32_t c[4][2];
+#pragma unroll
+          for (int m = 0; m < 4; ++m) fp8x4_to_h2x2<KV>(b[m], c[m][0], c[m][1]);
+          mma_16816<false>(s[2 * hb], qa[2 * jj], c[0][0], c[0][1]);
+          mma_16816<false>(s[2 * hb + 1], qa[2 * jj], c[1][0], c[1][1]);
+          mma_16816<false>(s[2 * hb], qa[2 * jj + 1], c[2][0], c[2][1]);
+          mma_16816<false>(s[2 * hb + 1], qa[2 * jj + 1], c[3][0], c[3][1]);
         }
       }
     }
@@ -323,7 +340,7 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
       for (int e = 0; e < NE; ++e) {
         float v = use_cap ? cap_l2 * fast_tanh(s[nt][e] * sc_nat * cap_inv) : s[nt][e] * sc;
         if (need_mask) {
-          const int tok = tok0 + nt * 8 + 2 * t + (e & 1);
+          const int tok = kFp8 ? tok0 + 16 * (nt >> 1) + 4 * t + 2 * (nt & 1) + (e & 1) : tok0 + nt * 8 + 2 * t + (e & 1);
           if (tok >= len || tok < lo) v = -INFINITY;
         }
         s[nt][e] = v;
@@ -397,27 +414,24 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
         mma_16816<kBf16>(o[2 * j + 1], pa, b[2], b[3]);
       }
     } else {
-      // One transposed 8x8(b16) matrix = 8 tokens x 16 fp8 columns.  After the
-      // transpose a thread holds tokens (2t, 2t+1) x columns (2g, 2g+1); the even
-      // / odd column of every pair feeds a separate n-tile (d = 16c + 2n + par).
+      // ldmatrix.m16n16.trans.b8 hands every thread four consecutive tokens of one d column per register: two
+      // converts make the B fragment of one n-tile, no byte permutes (the k index of the MMA runs over the
+      // tokens in the order 4t, 4t+1 | 4t+2, 4t+3, which is how the S accumulators hold them, see k_tok).
+      const int vrow = lane & 15, vmat = lane >> 4;
 #pragma unroll
       for (int hb = 0; hb < NBOX; ++hb) {
         uint32_t pa[4];
         pack_p(hb, pa);
 #pragma unroll
-        for (int jj = 0; jj < KS / 2; ++jj) {
-          const int dch = 2 * jj + v_cof;
+        for (int jj = 0; jj < D / 32; ++jj) {  // 32 d columns = n-tiles 4jj .. 4jj+3
+          const int dch = 2 * jj + vmat;       // 16-byte column
           uint32_t b[4];
-          ldmatrix_x4_trans(b, vbase + hb * Cfg::BOX_BYTES + (dch >> 3) * SUB + v_tok * 128 + (((dch & 7) ^ lr) << 4));
+          ldmatrix_b8_x2_trans(b, vbase + hb * Cfg::BOX_BYTES + (dch >> 3) * SUB + vrow * 128 + (((dch & 7) ^ (vrow & 7)) << 4));
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {  // 16-byte column 2jj + h
-            const uint32_t lo_t = b[2 * h], hi_t = b[2 * h + 1];  // tokens 0-7 / 8-15
-            const uint32_t be0 = fp8x2_to_h2<KV>(__byte_perm(lo_t, 0, 0x0020));
-            const uint32_t be1 = fp8x2_to_h2<KV>(__byte_perm(hi_t, 0, 0x0020));
-            const uint32_t bo0 = fp8x2_to_h2<KV>(__byte_perm(lo_t, 0, 0x0031));
-            const uint32_t bo1 = fp8x2_to_h2<KV>(__byte_perm(hi_t, 0, 0x0031));
-            mma_16816<false>(o[2 * (2 * jj + h)], pa, be0, be1);
-            mma_16816<false>(o[2 * (2 * jj + h) + 1], pa, bo0, bo1);
+          for (int qd = 0; qd < 4; ++qd) {
+            uint32_t c0, c1;
+            fp8x4_to_h2x2<KV>(b[qd], c0, c1);
+            mma_16816<false>(o[4 * jj + qd], pa, c0, c1);
           }
         }
       }
@@ -452,14 +466,7 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
     float* r_hi = sm_o + (warp * 16 + g + 8) * OPAD;
 #pragma unroll
     for (int n = 0; n < 2 * KS; ++n) {
-      int d0, d1;
-      if constexpr (kFp8) {
-        d0 = 16 * (n >> 1) + 4 * t + (n & 1);
-        d1 = d0 + 2;
-      } else {
-        d0 = n * 8 + 2 * t;
-        d1 = d0 + 1;
-      }
+      const int d0 = n * 8 + 2 * t, d1 = d0 + 1;
       r_lo[d0] = o[n][0];
       r_lo[d1] = o[n][1];
       if (rows > 8) {

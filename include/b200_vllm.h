@@ -147,6 +147,10 @@ size_t b200_paged_decode_workspace_bytes(int num_seqs, int num_q_heads,
                                          int head_size, int num_splits);
 int b200_paged_decode_pick_splits(int num_seqs, int num_kv_heads,
                                   int max_seq_len, int sm_count);
+/* The same with the cache geometry (resident CTAs per SM depend on it); the 4-argument form assumes
+ * head_size 128 with an fp8 cache. */
+int b200_paged_decode_pick_splits_ex(int num_seqs, int num_kv_heads, int max_seq_len, int sm_count,
+                                     int head_size, int kv_dtype);
 int b200_paged_attention_decode(const b200_paged_decode_params* p,
                                 b200_stream_t stream);
 

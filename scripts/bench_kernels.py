@@ -172,7 +172,7 @@ def bench_attention(ref: bool):
         q = torch.randn(B, Hq, D, device=DEV).to(torch.bfloat16)
         out = torch.empty_like(q)
         sc = torch.tensor([0.05], device=DEV)
-        splits = ops.paged_decode_num_splits(B, Hq, Hkv, ctx, DEV)
+        splits = ops.paged_decode_num_splits(B, Hq, Hkv, ctx, DEV, D, kvd)
         wsb = ops.paged_decode_workspace_bytes(B, Hq, D, splits)
         wsp = torch.empty(max(wsb, 16), dtype=torch.uint8, device=DEV)
         fns = [(lambda i=i: ops.paged_attention_decode(out, q, caches[i][0], caches[i][1], bt, sl, D ** -0.5, ctx, kvd,

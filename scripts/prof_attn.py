@@ -24,7 +24,7 @@ sl = torch.full((B,), ctx, device=DEV, dtype=torch.int32)
 q = torch.randn(B, Hq, D, device=DEV).to(torch.bfloat16)
 out = torch.empty_like(q)
 sc = torch.tensor([0.05], device=DEV)
-splits = a.splits or ops.paged_decode_num_splits(B, Hq, Hkv, ctx, DEV)
+splits = a.splits or ops.paged_decode_num_splits(B, Hq, Hkv, ctx, DEV, D, "fp8")
 ws = torch.empty(max(ops.paged_decode_workspace_bytes(B, Hq, D, splits), 16), dtype=torch.uint8, device=DEV)
 f = lambda: ops.paged_attention_decode(out, q, kv[0], kv[1], bt, sl, D ** -0.5, ctx, "fp8", sc, sc,
                                        num_splits=splits, workspace=ws)

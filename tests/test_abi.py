@@ -81,7 +81,7 @@ def test_split_heuristic_and_workspace(lib):
     # deterministic in its arguments only (CUDA-graph safe), >= 1, bounded
     s = lib.b200_paged_decode_pick_splits(64, 8, 4096, 148)
     assert s == lib.b200_paged_decode_pick_splits(64, 8, 4096, 148) and 1 <= s <= 128
-    assert lib.b200_paged_decode_pick_splits(4096, 8, 4096, 148) == 1     # plenty of CTAs already
+    assert lib.b200_paged_decode_pick_splits(4096, 8, 4096, 148) <= 2     # plenty of CTAs already
     assert lib.b200_paged_decode_pick_splits(16, 8, 131072, 148) > 8      # cfg5: long context needs many splits
     assert lib.b200_paged_decode_pick_splits(1, 1, 16, 148) == 1          # one chunk cannot be split
     assert lib.b200_paged_decode_workspace_bytes(64, 32, 128, 1) == 0

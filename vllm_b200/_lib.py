@@ -49,6 +49,7 @@ SIGNATURES: dict[str, tuple] = {
     "b200_compute_slot_mapping": (i32, [vp, i64, i64, vp, i32, vp, vp, i64, i32, vp]),
     "b200_paged_decode_workspace_bytes": (sz, [i32, i32, i32, i32]),
     "b200_paged_decode_pick_splits": (i32, [i32, i32, i32, i32]),
+    "b200_paged_decode_pick_splits_ex": (i32, [i32, i32, i32, i32, i32, i32]),
     "b200_paged_attention_decode": (i32, [C.POINTER(PagedDecodeParams), vp]),
     "b200_merge_attn_states": (i32, [vp, vp, vp, vp, vp, vp, i64, i32, i32, i64, i64, i64, i64, i64, i64, i64,
                                      i32, vp]),

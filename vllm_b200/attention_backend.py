@@ -91,6 +91,8 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         self.num_heads_kv = mc.get_num_kv_heads(pc)
         self.head_size = mc.get_head_size()
         self.max_model_len = mc.max_model_len
+        spec_dtype = getattr(kv_cache_spec, "dtype", None)
+        self._kv_kind = "fp8" if (spec_dtype is not None and torch.empty(0, dtype=spec_dtype).element_size() == 1) else "auto"
         sc = vllm_config.scheduler_config
         self.max_tokens = max(int(getattr(sc, "max_num_batched_tokens", 0) or 0), int(getattr(sc, "max_num_seqs", 0) or 0), 1)
         # persistent split-KV workspace sized for the worst (num_tokens, splits) the heuristic can pick
@@ -101,14 +103,21 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
         self._arange = torch.arange(self.max_tokens, dtype=torch.int32, device=device)
 
     def _splits(self, num_tokens: int, max_seq_len: int) -> int:
-        return ops.paged_decode_num_splits(num_tokens, self.num_heads_q, self.num_heads_kv, max_seq_len, self.device)
+        s = ops.paged_decode_num_splits(num_tokens, self.num_heads_q, self.num_heads_kv, max_seq_len, self.device,
+                                        self.head_size, self._kv_kind)
+        ws = getattr(self, "workspace", None)
+        if ws is not None:  # never outgrow the persistent workspace (graph-captured address)
+            while s > 1 and ops.paged_decode_workspace_bytes(num_tokens, self.num_heads_q, self.head_size, s) > ws.numel():
+                s -= 1
+        return s
 
     def _max_workspace_bytes(self) -> int:
         need, t = 16, 1
-        while True:  # splits(t) is non-increasing in t: probe powers of two and their neighbours
-            for tt in {t, min(self.max_tokens, 2 * t - 1)}:
-                s = self._splits(tt, self.max_model_len)
-                need = max(need, ops.paged_decode_workspace_bytes(tt, self.num_heads_q, self.head_size, s))
+        while True:  # probe powers of two and their neighbours; `_splits` clamps to the buffer afterwards
+            for tt in {t, min(self.max_tokens, 2 * t - 1), min(self.max_tokens, t + t // 2)}:
+                for msl in {self.max_model_len, max(256, self.max_model_len // 4)}:
+                    s = self._splits(tt, msl)
+                    need = max(need, ops.paged_decode_workspace_bytes(tt, self.num_heads_q, self.head_size, s))
             if t >= self.max_tokens:
                 break
             t = min(2 * t, self.max_tokens)

@@ -44,7 +44,10 @@ template <int D, int KV> struct DecodeCfg {
   static constexpr int BOX_BYTES = NSUB * SUB_BYTES;  // one 16-token piece of K (or V)
   static constexpr int KCH_BYTES = NBOX * BOX_BYTES;
   static constexpr int SLOT_BYTES = 2 * KCH_BYTES;  // K part + V part
-  static constexpr int NSLOT = (KV != B200_KV_AUTO) ? 2 : (ROWB >= 512 ? 2 : (ROWB == 256 ? 3 : 4));
+#ifndef B200_FP8_NSLOT
+#define B200_FP8_NSLOT 2
+#endif
+  static constexpr int NSLOT = (KV != B200_KV_AUTO) ? (ROWB >= 256 ? 2 : B200_FP8_NSLOT) : (ROWB >= 512 ? 2 : (ROWB == 256 ? 3 : 4));
   static constexpr int RING_BYTES = kWarps * NSLOT * SLOT_BYTES;
   static constexpr int OPAD = D + 8;  // fp32 row pitch of the merge buffer
   static constexpr int EPI_BYTES = kWarps * 16 * OPAD * 4 + 2 * kWarps * 16 * 4;
@@ -639,21 +642,43 @@ extern "C" size_t b200_paged_decode_workspace_bytes(int num_seqs, int num_q_head
   return (size_t)num_seqs * num_q_heads * num_splits * ((size_t)head_size * 4 + 8);
 }
 
-extern "C" int b200_paged_decode_pick_splits(int num_seqs, int num_kv_heads, int max_seq_len, int sm_count) {
-  // Deterministic in its arguments only (CUDA-graph safe).  Aim for ~8 waves of
-  // 2 resident CTAs per SM so the tail is <~10% while every split still streams
-  // at least 16 chunks (256 tokens) to amortise its prologue/merge.
+extern "C" int b200_paged_decode_pick_splits_ex(int num_seqs, int num_kv_heads, int max_seq_len, int sm_count,
+                                                int head_size, int kv_dtype) {
+  // Deterministic in its arguments only (CUDA-graph safe).  Model fitted to the split sweeps in
+  // profiles/r01_attn_splits.md: a CTA costs ~128 tokens' worth of prologue + merge, and the grid runs in
+  // rounds of (resident CTAs per SM) x SMs, so efficiency(s) = fill(base*s / slots) * work / (work + 128).
   if (sm_count <= 0) sm_count = 148;
+  static const int force = [] {
+    const char* e = getenv("B200_ATTN_SPLITS");  // tuning aid
+    return (e && *e) ? atoi(e) : 0;
+  }();
+  if (force > 0) return force;
   const long base = (long)num_seqs * num_kv_heads;
   if (base <= 0) return 1;
-  const int chunks = (max_seq_len + b200::kChunk - 1) / b200::kChunk;
-  long want = (8L * 2 * sm_count + base - 1) / base;
-  long cap = chunks / 16;
+  const int row_bytes = head_size * (kv_dtype == B200_KV_AUTO ? 2 : 1);
+  const int per_sm = (kv_dtype == B200_KV_AUTO) ? (row_bytes <= 128 ? 3 : (row_bytes == 256 ? 2 : 1))
+                                                : (row_bytes <= 128 ? 3 : 1);
+  const double slots = (double)per_sm * sm_count;
+  int cap = max_seq_len / 256;  // every split streams at least 256 tokens
+  if (cap > 128) cap = 128;
   if (cap < 1) cap = 1;
-  long s = want < cap ? want : cap;
-  if (s > 128) s = 128;
-  if (s < 1) s = 1;
-  return (int)s;
+  int best = 1;
+  double best_eff = -1.0;
+  for (int s = 1; s <= cap; ++s) {
+    const double waves = (double)base * s / slots;
+    const double fill = waves / (double)(long)(waves + 0.999999);
+    const double work = (double)max_seq_len / s;
+    const double eff = fill * work / (work + 128.0);
+    if (eff > best_eff * 1.01) {  // prefer fewer splits on near-ties
+      best_eff = eff;
+      best = s;
+    }
+  }
+  return best;
+}
+
+extern "C" int b200_paged_decode_pick_splits(int num_seqs, int num_kv_heads, int max_seq_len, int sm_count) {
+  return b200_paged_decode_pick_splits_ex(num_seqs, num_kv_heads, max_seq_len, sm_count, 128, B200_KV_FP8_E4M3);
 }
 
 extern "C" int b200_paged_attention_decode(const b200_paged_decode_params* p, b200_stream_t stream) {
@@ -716,8 +741,9 @@ extern "C" int b200_paged_attention_decode(const b200_paged_decode_params* p, b2
   a.soft_cap = p->logits_soft_cap;
   int splits = p->num_splits;
   if (splits <= 0)
-    splits = b200_paged_decode_pick_splits(p->num_seqs, p->num_kv_heads * a.qgroups,
-                                           p->max_seq_len > 0 ? p->max_seq_len : 1, sm_count());
+    splits = b200_paged_decode_pick_splits_ex(p->num_seqs, p->num_kv_heads * a.qgroups,
+                                              p->max_seq_len > 0 ? p->max_seq_len : 1, sm_count(), p->head_size,
+                                              p->kv_dtype);
   a.num_splits = splits;
   a.eff_splits = splits;
   a.max_seq_len = p->max_seq_len;

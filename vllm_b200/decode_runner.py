@@ -116,7 +116,8 @@ class DecodeRunner:
         self.block_table = torch.zeros(batch, self.blocks_per_seq, dtype=torch.int32, device=self.dev)
         self.query_start_loc = torch.arange(batch + 1, dtype=torch.int32, device=self.dev)
         self.next_tokens = torch.zeros(batch, dtype=torch.int64, device=self.dev)
-        self.num_splits = ops.paged_decode_num_splits(batch, self.Hq, self.Hkv, max_ctx, self.dev)
+        self.num_splits = ops.paged_decode_num_splits(batch, self.Hq, self.Hkv, max_ctx, self.dev, self.D,
+                                                      kv_cache_dtype if kv_cache_dtype.startswith("fp8") else "auto")
         ws = ops.paged_decode_workspace_bytes(batch, self.Hq, self.D, self.num_splits)
         self.attn_ws = torch.empty(max(ws, 16), dtype=torch.uint8, device=self.dev)
         self.scale = self.D ** -0.5

@@ -129,11 +129,13 @@ def compute_slot_mapping(
 
 # ----------------------------------------------------------------- paged attention decode
 def paged_decode_num_splits(num_seqs: int, num_q_heads: int, num_kv_heads: int, max_seq_len: int,
-                            device: torch.device | None = None) -> int:
+                            device: torch.device | None = None, head_size: int = 128,
+                            kv_cache_dtype: str = "auto") -> int:
     group = num_q_heads // num_kv_heads
     qgroups = (group + 15) // 16
     sm = torch.cuda.get_device_properties(device).multi_processor_count if torch.cuda.is_available() else 148
-    return int(_lib.load().b200_paged_decode_pick_splits(num_seqs, num_kv_heads * qgroups, max(1, max_seq_len), sm))
+    return int(_lib.load().b200_paged_decode_pick_splits_ex(num_seqs, num_kv_heads * qgroups, max(1, max_seq_len), sm,
+                                                            head_size, kv_dtype_code(kv_cache_dtype)))
 
 
 def paged_decode_workspace_bytes(num_seqs: int, num_q_heads: int, head_size: int, num_splits: int) -> int:
@@ -180,7 +182,8 @@ def paged_attention_decode(
     if kv == KV_AUTO and key_cache.dtype != query.dtype:
         raise RuntimeError("paged_attention_decode: kv_cache_dtype='auto' needs cache dtype == query dtype")
     if num_splits <= 0:
-        num_splits = paged_decode_num_splits(num_seqs, num_q_heads, num_kv_heads, max_seq_len, query.device)
+        num_splits = paged_decode_num_splits(num_seqs, num_q_heads, num_kv_heads, max_seq_len, query.device,
+                                             head_size, kv_cache_dtype)
     need = paged_decode_workspace_bytes(num_seqs, num_q_heads, head_size, num_splits)
     if need and (workspace is None or workspace.numel() * workspace.element_size() < need):
         workspace = torch.empty(need, dtype=torch.uint8, device=query.device)

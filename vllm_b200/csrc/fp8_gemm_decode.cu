@@ -752,7 +752,11 @@ int run_fp8_decode(void* out, const void* a, const void* b, const float* a_scale
   };
   int S3 = 0;
   if (force_mode < 0 || force_mode == 3) {
-    for (int S = 4; S >= 2; --S) {
+    static const int s_max = [] {
+      const char* e = getenv("B200_GEMM_SMAX");  // tuning aid: largest cluster split
+      return (e && *e) ? atoi(e) : 4;
+    }();
+    for (int S = s_max; S >= 2; --S) {
       if (d.num_kb / S < 2) continue;  // >= 2 k-blocks per split
       if (active_clusters(S) >= d.num_super) {
         S3 = S;

@@ -270,7 +270,9 @@ static int run_f4(void* out, const void* a, const void* b, const void* sfa, cons
   }
   g.sfx = reinterpret_cast<const uint8_t*>(sfa);
   g.sfy = reinterpret_cast<const uint8_t*>(sfb);
-  const int bn = N >= 2048 ? 256 : 128;
+  // 128x256 tiles unless that leaves SMs idle (few token rows): then twice as many 128x128 tiles
+  int bn = N >= 2048 ? 256 : 128;
+  if (bn == 256 && (long)((M + 127) / 128) * ((N + 255) / 256) < sm_count()) bn = 128;
   if ((rc = get_kmajor_tmap(&tx, a, M, kb, kb, 128))) return rc;
   if ((rc = get_kmajor_tmap(&ty, b, N, kb, kb, bn))) return rc;
   dim3 grid((M + 127) / 128, (N + bn - 1) / bn, 1);

@@ -28,14 +28,14 @@ namespace b200 {
 constexpr int kGemmThreads = 192;
 constexpr int kBK = 128;  // bytes of K per stage = one swizzle span (128 fp8 elements)
 
-template <int BN> struct GemmCfg {
+// kTwo: ring sized for TWO resident CTAs per SM (one CTA's epilogue overlaps the other's mainloop; the kernel is
+// not persistent).  Measured better for K <= 8192, worse for longer K where the deeper single-CTA ring wins.
+template <int BN, bool kTwo = false> struct GemmCfg {
   static constexpr int X_BYTES = 128 * kBK;
   static constexpr int Y_BYTES = BN * kBK;
   static constexpr int STAGE_BYTES = X_BYTES + Y_BYTES;
-#ifndef B200_GEMM_SMEM_KB
-#define B200_GEMM_SMEM_KB 200
-#endif
-  static constexpr int STAGES = (B200_GEMM_SMEM_KB * 1024) / STAGE_BYTES > 8 ? 8 : (B200_GEMM_SMEM_KB * 1024) / STAGE_BYTES;
+  static constexpr int RING_KB = kTwo ? 108 : 200;
+  static constexpr int STAGES = (RING_KB * 1024) / STAGE_BYTES > 8 ? 8 : (RING_KB * 1024) / STAGE_BYTES;
   static constexpr int TMEM_COLS = BN < 32 ? 32 : BN;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
@@ -87,11 +87,11 @@ template <> __device__ __forceinline__ void store16<__half>(__half* dst, const f
 
 // X rows -> TMEM lanes (128 per CTA), Y rows -> TMEM columns (BN per CTA).
 // kSwap == false: X = A (tokens, M), Y = B (weights, N).  kSwap == true: X = B, Y = A.
-template <int BN, bool kSwap, typename OutT>
-__global__ void __launch_bounds__(kGemmThreads, B200_GEMM_SMEM_KB <= 110 ? 2 : 1)
+template <int BN, bool kSwap, typename OutT, bool kTwo = false>
+__global__ void __launch_bounds__(kGemmThreads, kTwo ? 2 : 1)
     fp8_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_y,
                     const GemmArgs g) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, kTwo>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
@@ -305,11 +305,11 @@ int get_kmajor_tmap(CUtensorMap* out, const void* base, int rows, int k_bytes, i
   return 0;
 }
 
-template <int BN, bool kSwap, typename OutT>
+template <int BN, bool kSwap, typename OutT, bool kTwo = false>
 static int launch_fp8_gemm(const CUtensorMap& tx, const CUtensorMap& ty, const GemmArgs& g, dim3 grid,
                            cudaStream_t stream) {
-  using Cfg = GemmCfg<BN>;
-  auto kern = fp8_gemm_kernel<BN, kSwap, OutT>;
+  using Cfg = GemmCfg<BN, kTwo>;
+  auto kern = fp8_gemm_kernel<BN, kSwap, OutT, kTwo>;
   static bool attr = false;
   if (!attr) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
@@ -356,12 +356,21 @@ static int run_fp8_gemm(void* out, const void* a, const void* b, const float* a_
                                 b_scales_numel, workspace, workspace_bytes, stream);
   CUtensorMap tx, ty;
   int rc;
-  const int bn = (N % 256 == 0 || N > 2048) ? 256 : 128;
+  int bn = (N % 256 == 0 || N > 2048) ? 256 : 128;
+  {  // do not leave SMs idle: twice as many 128x128 tiles when they still fit in one wave of resident CTAs
+    const long mt = (M + 127) / 128, t256 = mt * ((N + 255) / 256), t128 = mt * ((N + 127) / 128);
+    const long resident = (long)sm_count() * (K <= 8192 ? 2 : 1);
+    if (bn == 256 && t256 < sm_count() && t128 <= resident) bn = 128;
+  }
   if ((rc = get_kmajor_tmap(&tx, a, M, K, lda, 128))) return rc;
   if ((rc = get_kmajor_tmap(&ty, b, N, K, ldb, bn))) return rc;
   dim3 grid((M + 127) / 128, (N + bn - 1) / bn, 1);
-  if (bn == 256) return launch_fp8_gemm<256, false, OutT>(tx, ty, g, grid, stream);
-  return launch_fp8_gemm<128, false, OutT>(tx, ty, g, grid, stream);
+  const bool two = K <= 8192;
+  if (bn == 256)
+    return two ? launch_fp8_gemm<256, false, OutT, true>(tx, ty, g, grid, stream)
+               : launch_fp8_gemm<256, false, OutT, false>(tx, ty, g, grid, stream);
+  return two ? launch_fp8_gemm<128, false, OutT, true>(tx, ty, g, grid, stream)
+             : launch_fp8_gemm<128, false, OutT, false>(tx, ty, g, grid, stream);
 }
 
 }  // namespace b200

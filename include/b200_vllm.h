@@ -327,6 +327,26 @@ int b200_rotary_embedding_and_cache_write(
     const float* k_scale, const float* v_scale, int kv_scale_stride, b200_stream_t stream);
 
 /* -------------------------------------------------------------------------
+ * In-place two-shot all-reduce (sum) over NVLink peer memory, for the row-parallel linears of a
+ * tensor-parallel step.  Replaces tensor_model_parallel_all_reduce (vllm/distributed/communication_op.py;
+ * the reference's small-message fast path is csrc/custom_all_reduce.cuh).
+ *   peer_buffers[world_size]      device addresses of every rank's buffer (same size, peer-mapped by the host,
+ *                                 e.g. torch symmetric memory); the tensor starts byte_offset into each
+ *   peer_signal_pads[world_size]  device addresses of every rank's zero-initialised signal pad
+ * numel 16-bit elements, multiple of 8 * world_size.  Every rank must call it in the same order.  The sum is
+ * taken in rank order with fp32 accumulation: identical on all ranks and run to run.
+ * ---------------------------------------------------------------------- */
+int b200_peer_all_reduce(const uint64_t* peer_buffers, const uint64_t* peer_signal_pads, int rank,
+                         int world_size, int64_t numel, int dtype, int64_t byte_offset,
+                         int64_t signal_pad_bytes, b200_stream_t stream);
+/* One-shot variant: every rank reads all buffers and writes the sum to its local `out` (the buffers are left
+ * untouched).  Needs only a start barrier, PROVIDED consecutive calls alternate between at least two buffers
+ * (byte_offset); meant for 2-4 ranks where reading (world-1) x the message is cheaper than a second barrier. */
+int b200_peer_all_reduce_out(void* out, const uint64_t* peer_buffers, const uint64_t* peer_signal_pads,
+                             int rank, int world_size, int64_t numel, int dtype, int64_t byte_offset,
+                             int64_t signal_pad_bytes, b200_stream_t stream);
+
+/* -------------------------------------------------------------------------
  * Programmatic dependent launch (no reference counterpart).  On by default (B200_PDL=0 in the
  * environment or b200_set_pdl(0) turns it off): every kernel is launched so that the next kernel's
  * prologue overlaps this kernel's tail, and every kernel waits for its predecessors' memory before

@@ -67,6 +67,8 @@ SIGNATURES: dict[str, tuple] = {
     "b200_silu_and_mul_dynamic_per_token_quant": (i32, [vp, vp, vp, i64, i32, i32, vp]),
     "b200_rotary_embedding_and_cache_write": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, i32, i32, i32, i32,
                                                     i64, i64, i64, i32, i64, i64, i64, i32, i32, vp, vp, i32, vp]),
+    "b200_peer_all_reduce": (i32, [vp, vp, i32, i32, i64, i32, i64, i64, vp]),
+    "b200_peer_all_reduce_out": (i32, [vp, vp, vp, i32, i32, i64, i32, i64, i64, vp]),
     "b200_set_pdl": (None, [i32]),
     "b200_get_pdl": (i32, []),
     "b200_debug_gemm_trace": (None, [vp]),

@@ -32,6 +32,7 @@ SOURCES = [
     "fp8_gemm.cu",
     "fp8_gemm_decode.cu",
     "nvfp4_gemm.cu",
+    "peer_allreduce.cu",
 ]
 
 NVCC_FLAGS = [

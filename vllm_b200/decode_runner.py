@@ -21,6 +21,8 @@ from __future__ import annotations
 
 import dataclasses
 import math
+import os
+import sys
 
 import torch
 import torch.distributed as dist
@@ -123,6 +125,18 @@ class DecodeRunner:
         self.scale = self.D ** -0.5
         self.graph: torch.cuda.CUDAGraph | None = None
         self.launches_per_step = 0
+        # Row-parallel partial sums: two-shot all-reduce over NVLink peer memory (b200_peer_all_reduce) on
+        # symmetric buffers the o_proj / down_proj GEMMs write into; NCCL when that cannot be set up.
+        self.par = None
+        if tp_size > 1 and self.wq == "fp8" and os.environ.get("B200_PEER_ALLREDUCE", "1") != "0":
+            try:
+                from .peer_comm import PeerAllReduce
+
+                self.par = PeerAllReduce(tp_group if tp_group is not None else dist.group.WORLD, self.dev, 2,
+                                         batch * shape.hidden, self.dtype)
+            except Exception as e:  # noqa: BLE001 - any failure here just means NCCL is used
+                print(f"[decode_runner] peer all-reduce unavailable ({e!r}); using NCCL", file=sys.stderr, flush=True)
+                self.par = None
 
     # ----------------------------------------------------------------- weights / linears
     def _quant_weight(self, w: torch.Tensor):
@@ -163,8 +177,19 @@ class DecodeRunner:
         self.input_ids.copy_(torch.randint(0, self.s.vocab, (self.B,), device=self.dev, generator=g))
         ops.compute_slot_mapping(self.query_start_loc, self.positions, self.block_table, self.bs, self.slot_mapping)
 
-    def _mm_fp8(self, xq: torch.Tensor, xs: torch.Tensor, lw) -> torch.Tensor:
-        return ops.cutlass_scaled_mm(xq, lw["w"].t(), xs, lw["s"], self.dtype)
+    def _mm_fp8(self, xq: torch.Tensor, xs: torch.Tensor, lw, out: torch.Tensor | None = None) -> torch.Tensor:
+        return ops.cutlass_scaled_mm(xq, lw["w"].t(), xs, lw["s"], self.dtype, out=out)
+
+    def _row_parallel_fp8(self, xq: torch.Tensor, xs: torch.Tensor, lw, which: int) -> torch.Tensor:
+        """Row-parallel linear + sum over the ranks (o_proj: which = 0, down_proj: which = 1)."""
+        if self.par is None:
+            return self._all_reduce(self._mm_fp8(xq, xs, lw))
+        out = self.par.view(which, self.B, self.s.hidden)
+        self._mm_fp8(xq, xs, lw, out=out)
+        if self.tp <= 4:  # one-shot: (tp-1) MB of peer reads beat a second cross-GPU barrier; o/down alternate buffers
+            return self.par.all_reduce_out(which, torch.empty_like(out))
+        self.par.all_reduce_(which)
+        return out
 
     def step_eager(self) -> torch.Tensor:
         s, B = self.s, self.B
@@ -192,12 +217,16 @@ class DecodeRunner:
             ops.paged_attention_decode(attn_out, q.view(B, self.Hq, self.D), kc, vc, self.block_table, self.seq_lens,
                                        self.scale, self.max_ctx, self.kv_dtype, self.k_scale, self.v_scale,
                                        num_splits=self.num_splits, workspace=self.attn_ws)
-            hidden = self._all_reduce(self._linear(attn_out.view(B, -1), lw["o"]))
+            if fused and self.par is not None:
+                oq, o_s = ops.scaled_fp8_quant(attn_out.view(B, -1), use_per_token_if_dynamic=True)
+                hidden = self._row_parallel_fp8(oq, o_s, lw["o"], 0)
+            else:
+                hidden = self._all_reduce(self._linear(attn_out.view(B, -1), lw["o"]))
             if fused:
                 xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, lw["ln2"], s.rms_eps, residual=residual)
                 gu = self._mm_fp8(xq, xs, lw["gate_up"])
                 aq, a_s = ops.silu_and_mul_dynamic_per_token_quant(gu)
-                hidden = self._all_reduce(self._mm_fp8(aq, a_s, lw["down"]))
+                hidden = self._row_parallel_fp8(aq, a_s, lw["down"], 1)
             else:
                 ops.fused_add_rms_norm(hidden, residual, lw["ln2"], s.rms_eps)
                 gu = self._linear(hidden, lw["gate_up"])

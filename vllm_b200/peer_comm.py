@@ -1,0 +1,70 @@
+"""Peer-memory all-reduce for tensor-parallel decode (host side).
+
+`PeerAllReduce` owns one symmetric-memory allocation per rank (torch.distributed._symmetric_memory: every rank can
+address every other rank's buffer over NVLink) and runs `b200_peer_all_reduce` on views of it.  The row-parallel
+GEMMs write their partial sums straight into the views, the kernel reduces in place, and the consumer reads the
+same view - no staging copies.  Mirrors what the reference's `CustomAllreduce`
+(vllm/distributed/device_communicators/custom_all_reduce.py) does for small messages.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+
+class PeerAllReduce:
+    def __init__(self, group, device: torch.device, num_buffers: int, numel: int, dtype: torch.dtype = torch.bfloat16):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        if dtype not in (torch.bfloat16, torch.float16):
+            raise RuntimeError("PeerAllReduce: 16-bit floating point tensors only")
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if numel % (8 * self.world):
+            raise RuntimeError(f"PeerAllReduce: numel {numel} must be a multiple of 8 * world_size")
+        self.dtype, self.numel, self.num_buffers = dtype, numel, num_buffers
+        self.storage = symm_mem.empty(num_buffers * numel, dtype=dtype, device=device)
+        self.handle = symm_mem.rendezvous(self.storage, group)
+        self.storage.zero_()
+        bufs = [int(p) for p in self.handle.buffer_ptrs]
+        pads = [int(p) for p in self.handle.signal_pad_ptrs]
+        self._bufs = (C.c_uint64 * self.world)(*bufs)
+        self._pads = (C.c_uint64 * self.world)(*pads)
+        self._pad_bytes = int(self.handle.signal_pad_size)
+        self._dt = 2 if dtype == torch.bfloat16 else 1  # B200_DT_BF16 / B200_DT_F16
+        torch.cuda.synchronize(device)
+        dist.barrier(group)
+
+    def view(self, index: int, *shape: int) -> torch.Tensor:
+        """The `index`-th buffer as a tensor of `shape` (the GEMM's `out=`)."""
+        n = 1
+        for d in shape:
+            n *= d
+        if n != self.numel or not 0 <= index < self.num_buffers:
+            raise RuntimeError("PeerAllReduce.view: shape/index does not match the allocation")
+        return self.storage[index * self.numel:(index + 1) * self.numel].view(*shape)
+
+    def all_reduce_out(self, index: int, out: torch.Tensor) -> torch.Tensor:
+        """One-shot sum of buffer `index` over the ranks into the local tensor `out`.  Consecutive calls must
+        alternate between buffers (see b200_peer_all_reduce_out)."""
+        from .ops import _stream
+
+        if out.numel() != self.numel or out.dtype != self.dtype or not out.is_contiguous():
+            raise RuntimeError("PeerAllReduce.all_reduce_out: out must be a contiguous tensor of the buffer's size/dtype")
+        rc = _lib.load().b200_peer_all_reduce_out(out.data_ptr(), self._bufs, self._pads, self.rank, self.world,
+                                                  self.numel, self._dt, index * self.numel * 2, self._pad_bytes,
+                                                  _stream(self.storage))
+        _lib.check(rc, "peer_all_reduce_out")
+        return out
+
+    def all_reduce_(self, index: int) -> None:
+        """Sum buffer `index` over the ranks, in place, on the current stream."""
+        from .ops import _stream
+
+        rc = _lib.load().b200_peer_all_reduce(self._bufs, self._pads, self.rank, self.world, self.numel, self._dt,
+                                              index * self.numel * 2, self._pad_bytes, _stream(self.storage))
+        _lib.check(rc, "peer_all_reduce")

@@ -148,7 +148,7 @@ def run_reference(args) -> None:
 
 
 # per-launch DRAM traffic of the dominant kernel at the default workload (ncu capture committed under profiles/)
-NCU_ATTN_DRAM_BYTES = 1_075_023_000 + 6_118_656
+NCU_ATTN_DRAM_BYTES = 1_074_973_000 + 8_505_088
 
 # ------------------------------------------------------------------------------ our arm
 def run_ours(args) -> None:
@@ -304,7 +304,7 @@ def run_ours(args) -> None:
                          "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "frac_of_8TBps_nameplate": achieved / 8000.0,
                          "traffic": NCU_ATTN_DRAM_BYTES if (world == 1 and B == 128 and ctx == 4096) else None,
                          "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full, "
-                                           "profiles/r01_decode_fp8_full_v2.txt (same workload, TP1)",
+                                           "profiles/r01_decode_fp8_full_v3.txt (same workload, TP1)",
                          "algorithmic_bytes_per_launch": attn_bytes, "ms_per_launch": attn_ms},
             "step_model": {"algorithmic_bytes_per_step": step_bytes, "hbm_frac_of_step": step_bytes / (ms_dev * 1e-3) / 1e9 / pk["hbm_gbs"]},
         }

@@ -208,11 +208,16 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
       a.block_table + (int64_t)(a.token_to_seq ? a.token_to_seq[seq] : seq) * a.block_table_stride;
   // block id of 16-token piece h of this lane's slot in `batch` (0 where the piece starts past the sequence:
   // such a piece is not loaded, and the table may not extend that far)
+  // block_size is a power of two in practice (16..128): shift/mask instead of the ~20-instruction integer
+  // division, which sat in the per-slot TMA issue path of every warp
+  const int bs_shift = (a.block_size & (a.block_size - 1)) == 0 ? 31 - __clz(a.block_size) : -1;
+  auto div_bs = [&](int tok) { return bs_shift >= 0 ? (tok >> bs_shift) : tok / a.block_size; };
+  auto mod_bs = [&](int tok) { return bs_shift >= 0 ? (tok & (a.block_size - 1)) : tok % a.block_size; };
   auto load_id = [&](int batch, int h) -> int {
     const int i = batch * 32 + lane;
     if (i < n_my) {
       const int tok = (c0 + warp + kWarps * i) * TOK + h * kChunk;
-      if (tok < len) return bt_row[tok / a.block_size];
+      if (tok < len) return bt_row[div_bs(tok)];
     }
     return 0;
   };
@@ -245,7 +250,7 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
 #pragma unroll
       for (int h = 0; h < NBOX; ++h) {
         if (tok0 + h * kChunk >= len) continue;
-        const int tok_in_blk = (tok0 + h * kChunk) % a.block_size;
+        const int tok_in_blk = mod_bs(tok0 + h * kChunk);
 #pragma unroll
         for (int sb = 0; sb < Cfg::NSUB; ++sb)
           tma_load_4d(dst + h * Cfg::BOX_BYTES + sb * SUB, &tmap_k, &wbar[slot], sb * Cfg::BOX_D, kvh, tok_in_blk,

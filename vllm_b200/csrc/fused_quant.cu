@@ -99,10 +99,28 @@ __global__ void __launch_bounds__(1024) rms_norm_quant_kernel(uint8_t* __restric
   ss = block_reduce<false>(ss, sh);
   const float rms = rsqrtf(ss / hidden + eps);
   float amax = 0.f;
-  for (int e = threadIdx.x; e < hidden; e += blockDim.x) {
-    const float y = mul_round<T>(rowf[e] * rms, to_float(w[e]));
-    rowf[e] = y;
-    amax = fmaxf(amax, fabsf(y));
+  if (vec) {  // 8 elements per thread and access (the scalar loop was 8 dependent rounds of 2-byte weight loads)
+    for (int v = threadIdx.x; v < hidden / N; v += blockDim.x) {
+      const uint4 wr = *reinterpret_cast<const uint4*>(w + v * N);
+      const T* wv = reinterpret_cast<const T*>(&wr);
+      float* rp = rowf + v * N;
+#pragma unroll
+      for (int i = 0; i < N; i += 4) {
+        float4 x = *reinterpret_cast<const float4*>(rp + i);
+        x.x = mul_round<T>(x.x * rms, to_float(wv[i]));
+        x.y = mul_round<T>(x.y * rms, to_float(wv[i + 1]));
+        x.z = mul_round<T>(x.z * rms, to_float(wv[i + 2]));
+        x.w = mul_round<T>(x.w * rms, to_float(wv[i + 3]));
+        *reinterpret_cast<float4*>(rp + i) = x;
+        amax = fmaxf(amax, fmaxf(fmaxf(fabsf(x.x), fabsf(x.y)), fmaxf(fabsf(x.z), fabsf(x.w))));
+      }
+    }
+  } else {
+    for (int e = threadIdx.x; e < hidden; e += blockDim.x) {
+      const float y = mul_round<T>(rowf[e] * rms, to_float(w[e]));
+      rowf[e] = y;
+      amax = fmaxf(amax, fabsf(y));
+    }
   }
   amax = block_reduce<true>(amax, sh);
   float s = scale_ub ? fminf(amax, *scale_ub) : amax;

@@ -522,27 +522,49 @@ __global__ void __launch_bounds__(128) paged_decode_combine_kernel(
     int64_t out_stride_seq, int64_t out_stride_head) {
   pdl_trigger();
   pdl_wait();
-  const int h = blockIdx.x, seq = blockIdx.y;
+  // one warp per (sequence, head), four heads per CTA; a lane owns 4 consecutive d (16-byte partial loads,
+  // all splits' loads independent of each other)
+  const int h = blockIdx.x * 4 + (threadIdx.x >> 5), seq = blockIdx.y, lane = threadIdx.x & 31;
+  if (h >= num_q_heads) return;
   const int64_t base = ((int64_t)seq * num_q_heads + h) * num_splits;
   float mt = -INFINITY;
-  for (int i = 0; i < num_splits; ++i) mt = fmaxf(mt, part_ml[base + i].x);
+  for (int i = lane; i < num_splits; i += 32) mt = fmaxf(mt, part_ml[base + i].x);
+  mt = warp_max(mt);
   float lt = 0.f;
-  for (int i = 0; i < num_splits; ++i) {
+  for (int i = lane; i < num_splits; i += 32) {
     const float2 ml = part_ml[base + i];
     lt += (ml.x == -INFINITY) ? 0.f : ml.y * fast_exp2(ml.x - mt);
   }
+  lt = warp_sum(lt);
   const float vs = v_scale ? *v_scale : 1.f;
   const float inv = lt > 0.f ? vs / lt : 0.f;
   QT* op = out + (int64_t)seq * out_stride_seq + (int64_t)h * out_stride_head;
-  for (int d = threadIdx.x; d < D; d += blockDim.x) {
-    float acc = 0.f;
-    for (int i = 0; i < num_splits; ++i) {
-      const float mi = part_ml[base + i].x;
-      if (mi != -INFINITY) acc += part_o[(base + i) * D + d] * fast_exp2(mi - mt);
+  const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(op) & 7) == 0);
+  if (vec) {
+    for (int d = lane * 4; d < D; d += 128) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int i = 0; i < num_splits; ++i) {
+        const float mi = part_ml[base + i].x;
+        if (mi == -INFINITY) continue;
+        const float wgt = fast_exp2(mi - mt);
+        const float4 p = *reinterpret_cast<const float4*>(part_o + (base + i) * D + d);
+        acc.x += p.x * wgt, acc.y += p.y * wgt, acc.z += p.z * wgt, acc.w += p.w * wgt;
+      }
+      QT r[4] = {from_float<QT>(acc.x * inv), from_float<QT>(acc.y * inv), from_float<QT>(acc.z * inv),
+                 from_float<QT>(acc.w * inv)};
+      *reinterpret_cast<uint2*>(op + d) = *reinterpret_cast<const uint2*>(r);
     }
-    op[d] = from_float<QT>(acc * inv);
+  } else {
+    for (int d = lane; d < D; d += 32) {
+      float acc = 0.f;
+      for (int i = 0; i < num_splits; ++i) {
+        const float mi = part_ml[base + i].x;
+        if (mi != -INFINITY) acc += part_o[(base + i) * D + d] * fast_exp2(mi - mt);
+      }
+      op[d] = from_float<QT>(acc * inv);
+    }
   }
-  if (threadIdx.x == 0 && out_lse)
+  if (lane == 0 && out_lse)
     out_lse[(int64_t)seq * num_q_heads + h] = lt > 0.f ? (mt + log2f(lt)) * kLn2 : -INFINITY;
 }
 
@@ -628,7 +650,7 @@ static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const Dec
     count_launch();
   }
   if (a.num_splits > 1) {
-    dim3 g2(a.num_q_heads, num_seqs);
+    dim3 g2((a.num_q_heads + 3) / 4, num_seqs);
     launch_kernel(paged_decode_combine_kernel<QT>, dim3(g2), dim3(128), 0, stream, 1, 
         reinterpret_cast<QT*>(a.out), a.out_lse, a.part_o, a.part_ml, KV == B200_KV_AUTO ? nullptr : a.v_scale,
         a.num_q_heads, a.num_splits, D, a.out_stride_seq, a.out_stride_head);

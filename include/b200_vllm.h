@@ -345,6 +345,15 @@ int b200_peer_all_reduce(const uint64_t* peer_buffers, const uint64_t* peer_sign
 int b200_peer_all_reduce_out(void* out, const uint64_t* peer_buffers, const uint64_t* peer_signal_pads,
                              int rank, int world_size, int64_t numel, int dtype, int64_t byte_offset,
                              int64_t signal_pad_bytes, b200_stream_t stream);
+/* One-shot all-reduce of a row-parallel GEMM output fused with what follows it in the decoder layer:
+ * residual += sum; result, scales = dynamic per-token FP8 quant of RMSNorm(residual) * weight
+ * (= b200_peer_all_reduce_out followed by b200_rms_norm_dynamic_per_token_quant with a residual, bit-identical to
+ * that composition).  Same buffer-alternation rule as b200_peer_all_reduce_out. */
+int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, const uint64_t* peer_buffers,
+                                        const uint64_t* peer_signal_pads, int rank, int world_size,
+                                        int64_t byte_offset, int64_t signal_pad_bytes, const void* weight,
+                                        void* residual, float epsilon, int64_t num_tokens, int hidden, int dtype,
+                                        b200_stream_t stream);
 
 /* -------------------------------------------------------------------------
  * Programmatic dependent launch (no reference counterpart).  On by default (B200_PDL=0 in the

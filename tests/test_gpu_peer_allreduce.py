@@ -42,6 +42,25 @@ def _worker(rank, world, port, q):
         allg = [torch.empty_like(got) for _ in range(world)]
         dist.all_gather(allg, got.contiguous())
         ok = ok and all(torch.equal(allg[0], t) for t in allg)  # identical on every rank
+    # fused all-reduce + residual add + RMSNorm + per-token FP8 quant == the two separate kernels, bit for bit
+    from vllm_b200 import ops
+
+    w = (torch.rand(H, device=dev, generator=g) + 0.5).to(torch.bfloat16)
+    dist.broadcast(w, 0)
+    for it in range(4):
+        x = torch.randn(B, H, device=dev, generator=g).to(torch.bfloat16)
+        res = torch.randn(B, H, device=dev, generator=torch.Generator(device=dev).manual_seed(100 + it)).to(torch.bfloat16)
+        par.view(it & 1, B, H).copy_(x)
+        summed = par.all_reduce_out(it & 1, torch.empty(B, H, device=dev, dtype=torch.bfloat16)).clone()
+        res_ref = res.clone()
+        xq_ref, xs_ref = ops.rms_norm_dynamic_per_token_quant(summed, w, 1e-5, residual=res_ref)
+        it2 = (it + 1) & 1
+        par.view(it2, B, H).copy_(x)
+        res_f = res.clone()
+        xq, xs = par.all_reduce_rms_norm_quant(it2, B, w, 1e-5, res_f)
+        torch.cuda.synchronize()
+        ok = ok and torch.equal(xq.view(torch.uint8), xq_ref.view(torch.uint8)) and torch.equal(xs, xs_ref)
+        ok = ok and torch.equal(res_f, res_ref)
     if rank == 0:
         q.put(ok)
     torch.cuda.synchronize()

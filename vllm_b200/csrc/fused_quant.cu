@@ -12,7 +12,7 @@
 //           bit-identical to rotary_embedding followed by reshape_and_cache_flash
 // One CTA per token row; the row lives in shared memory between the statistics pass and the convert pass,
 // so HBM/L2 sees every activation once; 16-byte vectors throughout.
-#include "common.cuh"
+#include "peer_sync.cuh"
 
 namespace b200 {
 
@@ -136,6 +136,86 @@ __global__ void __launch_bounds__(1024) rms_norm_quant_kernel(uint8_t* __restric
   } else {
     for (int e = threadIdx.x; e < hidden; e += blockDim.x) dst[e] = cvt_e4m3_sat(__fdiv_rn(rowf[e], s));
   }
+}
+
+// ---- (1b) the same fused with the tensor-parallel all-reduce that precedes it ------------------------------
+// hidden = sum over ranks of the row-parallel GEMM output (one-shot: every rank reads all peer buffers, rank order,
+// fp32 accumulation, rounded to T like the stand-alone all-reduce), then exactly kernel (1) with a residual.
+// One launch and one activation round trip less per row-parallel linear.  Start barrier only: the caller
+// alternates between two buffers (see b200_peer_all_reduce_out).
+template <typename T>
+__global__ void __launch_bounds__(1024) peer_allreduce_rms_norm_quant_kernel(
+    uint8_t* __restrict__ out, float* __restrict__ scales, const ArArgs a, const T* __restrict__ w,
+    T* __restrict__ residual, int num_tokens, int hidden, float eps) {
+  pdl_trigger();
+  pdl_wait();
+  constexpr int N = 8;
+  __shared__ float sh[32];
+  __shared__ uint32_t* s_pads[kArMaxWorld];
+  extern __shared__ __align__(16) uint8_t row_buf[];
+  float* rowf = reinterpret_cast<float*>(row_buf);
+  if ((int)threadIdx.x < a.world) s_pads[threadIdx.x] = a.pads[threadIdx.x];
+  uint32_t* my_epoch = a.pads[a.rank] + blockIdx.x * kArSlotWords + 2 * kArMaxWorld;
+  const uint32_t epoch = *my_epoch + 1;
+  ar_barrier(s_pads, a.rank, a.world, 0, epoch);
+  const int nv = hidden / N;
+  for (int row = blockIdx.x; row < num_tokens; row += gridDim.x) {
+    T* res = residual + (int64_t)row * hidden;
+    uint8_t* dst = out + (int64_t)row * hidden;
+    float ss = 0.f;
+    for (int v = threadIdx.x; v < nv; v += blockDim.x) {
+      uint4 in[kArMaxWorld];
+#pragma unroll
+      for (int q = 0; q < kArMaxWorld; ++q)
+        if (q < a.world) in[q] = reinterpret_cast<const uint4*>(a.bufs[q])[(int64_t)row * nv + v];
+      const uint4 rr = *reinterpret_cast<const uint4*>(res + v * N);
+      const T* rv = reinterpret_cast<const T*>(&rr);
+      float acc[N];
+#pragma unroll
+      for (int i = 0; i < N; ++i) acc[i] = 0.f;
+#pragma unroll
+      for (int q = 0; q < kArMaxWorld; ++q)
+        if (q < a.world) {
+          const T* e = reinterpret_cast<const T*>(&in[q]);
+#pragma unroll
+          for (int i = 0; i < N; ++i) acc[i] += to_float(e[i]);
+        }
+      uint4 o;
+      T* ov = reinterpret_cast<T*>(&o);
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        const float x = to_float(from_float<T>(acc[i])) + to_float(rv[i]);  // all-reduce output is T; then fused add
+        ov[i] = from_float<T>(x);
+        rowf[v * N + i] = x;
+        ss += x * x;
+      }
+      *reinterpret_cast<uint4*>(res + v * N) = o;
+    }
+    ss = block_reduce<false>(ss, sh);
+    const float rms = rsqrtf(ss / hidden + eps);
+    float amax = 0.f;
+    for (int v = threadIdx.x; v < nv; v += blockDim.x) {
+      const uint4 wr = *reinterpret_cast<const uint4*>(w + v * N);
+      const T* wv = reinterpret_cast<const T*>(&wr);
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        const float y = mul_round<T>(rowf[v * N + i] * rms, to_float(wv[i]));
+        rowf[v * N + i] = y;
+        amax = fmaxf(amax, fabsf(y));
+      }
+    }
+    amax = block_reduce<true>(amax, sh);
+    const float s = fmaxf(amax / kFp8MaxF, kMinScaleF);
+    if (threadIdx.x == 0) scales[row] = s;
+    for (int v = threadIdx.x; v < hidden / 4; v += blockDim.x) {
+      const float4 y = *reinterpret_cast<const float4*>(rowf + v * 4);
+      const uint32_t qv = cvt_e4m3_sat(__fdiv_rn(y.x, s)) | (cvt_e4m3_sat(__fdiv_rn(y.y, s)) << 8) |
+                          (cvt_e4m3_sat(__fdiv_rn(y.z, s)) << 16) | (cvt_e4m3_sat(__fdiv_rn(y.w, s)) << 24);
+      *reinterpret_cast<uint32_t*>(dst + v * 4) = qv;
+    }
+    __syncthreads();  // rowf is reused by the next row
+  }
+  if (threadIdx.x == 0) *my_epoch = epoch;
 }
 
 // ---- (2) ---------------------------------------------------------------------------------
@@ -413,6 +493,50 @@ extern "C" int b200_rotary_embedding_and_cache_write(
     else if (kv_dtype == B200_KV_FP8_E4M3) B200_RC(B200_KV_FP8_E4M3);
     else B200_RC(B200_KV_FP8_E5M2);
 #undef B200_RC
+    B200_CHECK_LAUNCH();
+    count_launch();
+    return 0;
+  });
+}
+
+extern "C" int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, const uint64_t* peer_buffers,
+                                                   const uint64_t* peer_signal_pads, int rank, int world_size,
+                                                   int64_t byte_offset, int64_t signal_pad_bytes, const void* weight,
+                                                   void* residual, float epsilon, int64_t num_tokens, int hidden,
+                                                   int dtype, b200_stream_t stream) {
+  using namespace b200;
+  B200_CHECK_ARG(result && scales && peer_buffers && peer_signal_pads && weight && residual, B200_ERR_INVALID_ARG,
+                 "peer_all_reduce_rms_norm_quant: null pointer");
+  B200_CHECK_ARG(world_size >= 2 && world_size <= kArMaxWorld && rank >= 0 && rank < world_size, B200_ERR_INVALID_ARG,
+                 "peer_all_reduce_rms_norm_quant: world size %d / rank %d not supported (2..8 ranks)", world_size, rank);
+  B200_CHECK_ARG(num_tokens > 0 && hidden > 0 && hidden % 8 == 0 && hidden <= 49152 && byte_offset % 16 == 0,
+                 B200_ERR_INVALID_ARG, "peer_all_reduce_rms_norm_quant: hidden must be a multiple of 8 (<= 49152)");
+  B200_CHECK_ARG(reinterpret_cast<uintptr_t>(weight) % 16 == 0 && reinterpret_cast<uintptr_t>(residual) % 16 == 0 &&
+                     reinterpret_cast<uintptr_t>(result) % 4 == 0,
+                 B200_ERR_ALIGNMENT, "peer_all_reduce_rms_norm_quant: weight/residual must be 16-byte aligned");
+  int64_t grid = num_tokens < 64 ? num_tokens : 64;
+  const int64_t max_grid = signal_pad_bytes / (kArSlotWords * 4);
+  if (grid > max_grid) grid = max_grid;
+  B200_CHECK_ARG(grid >= 1, B200_ERR_INVALID_ARG, "peer_all_reduce_rms_norm_quant: signal pad too small");
+  ArArgs a;
+  for (int q = 0; q < kArMaxWorld; ++q) {
+    a.bufs[q] = q < world_size ? reinterpret_cast<void*>(peer_buffers[q] + byte_offset) : nullptr;
+    a.pads[q] = q < world_size ? reinterpret_cast<uint32_t*>(peer_signal_pads[q]) : nullptr;
+  }
+  a.rank = rank;
+  a.world = world_size;
+  a.numel = num_tokens * hidden;
+  return dispatch16f(dtype, "peer_all_reduce_rms_norm_quant", [&](auto tag) {
+    using T = decltype(tag);
+    static bool attr = false;
+    if (!attr) {
+      cudaFuncSetAttribute(peer_allreduce_rms_norm_quant_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 49152 * 4);
+      attr = true;
+    }
+    const int threads = row_threads(hidden / 8);
+    launch_kernel(peer_allreduce_rms_norm_quant_kernel<T>, dim3((unsigned)grid), dim3(threads), hidden * 4,
+                  (cudaStream_t)stream, 1, (uint8_t*)result, scales, a, (const T*)weight, (T*)residual, (int)num_tokens,
+                  hidden, epsilon);
     B200_CHECK_LAUNCH();
     count_launch();
     return 0;

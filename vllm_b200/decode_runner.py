@@ -197,12 +197,20 @@ class DecodeRunner:
         residual = torch.zeros_like(hidden)
         attn_out = torch.empty(B, self.Hq, self.D, device=self.dev, dtype=self.dtype)
         fused = self.wq == "fp8" and self.fused
+        # TP <= 4: the all-reduce after a row-parallel GEMM is fused with the residual add + RMSNorm + FP8 quant
+        # that follows it (b200_peer_all_reduce_rms_norm_quant); `pending` = the down_proj partial sums of the
+        # previous layer still sit un-reduced in peer buffer 1
+        fuse_ar = fused and self.par is not None and self.tp <= 4
+        pending = False
         for lw, kv in zip(self.layers, self.kv_caches):
             kc, vc = kv.unbind(0)
             if fused:
                 # 10 launches per layer: norm+quant, GEMM, rope+cache, attention (+combine), quant, GEMM,
                 # norm+quant, GEMM, silu*mul+quant, GEMM
-                xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, lw["ln1"], s.rms_eps, residual=residual)
+                if pending:
+                    xq, xs = self.par.all_reduce_rms_norm_quant(1, B, lw["ln1"], s.rms_eps, residual)
+                else:
+                    xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, lw["ln1"], s.rms_eps, residual=residual)
                 qkv = self._mm_fp8(xq, xs, lw["qkv"])
                 q, k, v = qkv.split([self.Hq * self.D, self.Hkv * self.D, self.Hkv * self.D], dim=-1)
                 ops.rotary_embedding_and_cache_write(self.positions, q, k, v, self.D, self.cos_sin, kc, vc,
@@ -217,6 +225,15 @@ class DecodeRunner:
             ops.paged_attention_decode(attn_out, q.view(B, self.Hq, self.D), kc, vc, self.block_table, self.seq_lens,
                                        self.scale, self.max_ctx, self.kv_dtype, self.k_scale, self.v_scale,
                                        num_splits=self.num_splits, workspace=self.attn_ws)
+            if fuse_ar:
+                oq, o_s = ops.scaled_fp8_quant(attn_out.view(B, -1), use_per_token_if_dynamic=True)
+                self._mm_fp8(oq, o_s, lw["o"], out=self.par.view(0, B, s.hidden))
+                xq, xs = self.par.all_reduce_rms_norm_quant(0, B, lw["ln2"], s.rms_eps, residual)
+                gu = self._mm_fp8(xq, xs, lw["gate_up"])
+                aq, a_s = ops.silu_and_mul_dynamic_per_token_quant(gu)
+                self._mm_fp8(aq, a_s, lw["down"], out=self.par.view(1, B, s.hidden))
+                pending = True
+                continue
             if fused and self.par is not None:
                 oq, o_s = ops.scaled_fp8_quant(attn_out.view(B, -1), use_per_token_if_dynamic=True)
                 hidden = self._row_parallel_fp8(oq, o_s, lw["o"], 0)
@@ -233,6 +250,8 @@ class DecodeRunner:
                 act = torch.empty(B, self.inter, device=self.dev, dtype=self.dtype)
                 ops.silu_and_mul(act, gu)
                 hidden = self._all_reduce(self._linear(act, lw["down"]))
+        if pending:  # the last layer's down_proj: plain one-shot all-reduce, then the final norm
+            hidden = self.par.all_reduce_out(1, torch.empty(B, s.hidden, device=self.dev, dtype=self.dtype))
         ops.fused_add_rms_norm(hidden, residual, self.final_ln, s.rms_eps)
         logits = torch.matmul(hidden, self.lm_head.t())  # plain library GEMM (bf16 lm_head, as in vLLM)
         if self.tp == 1:

@@ -61,6 +61,24 @@ class PeerAllReduce:
         _lib.check(rc, "peer_all_reduce_out")
         return out
 
+    def all_reduce_rms_norm_quant(self, index: int, num_tokens: int, weight: torch.Tensor, epsilon: float,
+                                  residual: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+        """residual += sum over ranks of buffer `index` ([num_tokens, hidden]); returns the per-token FP8 quant of
+        RMSNorm(residual) * weight and its scales - one kernel (b200_peer_all_reduce_rms_norm_quant)."""
+        from .ops import _stream
+
+        hidden = self.numel // num_tokens
+        if hidden * num_tokens != self.numel or residual.shape != (num_tokens, hidden) or not residual.is_contiguous():
+            raise RuntimeError("PeerAllReduce.all_reduce_rms_norm_quant: shapes do not match the buffer")
+        xq = torch.empty(num_tokens, hidden, dtype=torch.float8_e4m3fn, device=residual.device)
+        xs = torch.empty(num_tokens, 1, dtype=torch.float32, device=residual.device)
+        rc = _lib.load().b200_peer_all_reduce_rms_norm_quant(
+            xq.data_ptr(), xs.data_ptr(), self._bufs, self._pads, self.rank, self.world, index * self.numel * 2,
+            self._pad_bytes, weight.data_ptr(), residual.data_ptr(), float(epsilon), num_tokens, hidden, self._dt,
+            _stream(self.storage))
+        _lib.check(rc, "peer_all_reduce_rms_norm_quant")
+        return xq, xs
+
     def all_reduce_(self, index: int) -> None:
         """Sum buffer `index` over the ranks, in place, on the current stream."""
         from .ops import _stream

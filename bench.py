@@ -147,8 +147,26 @@ def run_reference(args) -> None:
     print(json.dumps(line))
 
 
-# per-launch DRAM traffic of the dominant kernel at the default workload (ncu capture committed under profiles/)
-NCU_ATTN_DRAM_BYTES = 1_074_973_000 + 8_505_088
+def attn_traffic(world: int, B: int, ctx: int) -> tuple[float | None, str]:
+    """Per-launch DRAM bytes of the dominant kernel from the committed ncu capture (profiles/attn_traffic.json,
+    written by scripts/ncu_summary.py traffic) - only while the kernel sources are still the ones that were
+    profiled (digest match) and the workload is the profiled one; otherwise null."""
+    import hashlib
+
+    f = ROOT / "profiles" / "attn_traffic.json"
+    if not f.exists():
+        return None, "no profiles/attn_traffic.json"
+    rec = json.loads(f.read_text())
+    h = hashlib.sha256()
+    for name in ("paged_decode.cu", "paged_decode.cuh", "common.cuh"):
+        h.update((ROOT / "vllm_b200" / "csrc" / name).read_bytes())
+    if h.hexdigest()[:16] != rec.get("kernel_src_sha16"):
+        return None, "profiles/attn_traffic.json was captured from different kernel sources (digest mismatch)"
+    if not (world == 1 and B == 128 and ctx == 4096):
+        return None, "capture is for configs[2] TP1 only"
+    return rec["dram_bytes_per_launch"], (f"dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, "
+                                          f"profiles/attn_traffic.json (kernel sources {rec['kernel_src_sha16']})")
+
 
 # ------------------------------------------------------------------------------ our arm
 def run_ours(args) -> None:
@@ -255,7 +273,11 @@ def run_ours(args) -> None:
         e2e_step()
     e1.record()
     barrier()
-    ms_e2e = max_over_ranks(max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3 * 0.0)) / args.steps
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    # the caller-visible time: host wall clock around the loop (it includes the per-step stream synchronise);
+    # the device-side event span is reported beside it and can only be shorter
+    ms_e2e_dev = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    ms_e2e = max(max_over_ranks(wall_ms) / args.steps, ms_e2e_dev)
 
     # ---- dominant kernel (paged-attention decode) timed alone, CUDA events on its launch stream,
     #      cycling through the layers' distinct 1 GB caches so no launch finds its KV in L2
@@ -281,6 +303,23 @@ def run_ours(args) -> None:
     pk, pk_kind = peaks()
     achieved = attn_bytes / (attn_ms * 1e-3) / 1e9
 
+    traffic, traffic_src = attn_traffic(world, B, ctx)
+    # ---- untimed self-check at N > 1: does the TP=N step compute the TP=1 function?  (small 2-layer model built from
+    #      ONE seeded checkpoint and sharded through vllm_b200.tp_shard; every rank compares against its local TP=1 run)
+    tp_check = None
+    if world > 1 and not args.no_tp_check:
+        from vllm_b200.decode_runner import tp_equivalence_check
+
+        try:
+            res = tp_equivalence_check(world, rank, group, dev)
+        except Exception as e:  # noqa: BLE001 - reported, never fatal for the measurement
+            res = {"hidden_rel_l2": float("nan"), "tokens_equal_frac": 0.0, "peer_allreduce": None, "error": repr(e)}
+        allres = [None] * world
+        dist.all_gather_object(allres, res, group=group)
+        tp_check = {"errors": [r["error"] for r in allres if "error" in r],"hidden_rel_l2_max_over_ranks": max(r["hidden_rel_l2"] for r in allres),
+                    "tokens_equal_frac_min_over_ranks": min(r["tokens_equal_frac"] for r in allres),
+                    "peer_allreduce": res["peer_allreduce"], "bound_rel_l2": 0.05,
+                    "what": "TP=N vs TP=1 hidden state after the final norm, 2-layer Llama-shaped model, batch 16 x ctx 500"}
     if rank == 0:
         tok_s = B / (ms_dev * 1e-3)
         step_bytes = runner.L * (attn_bytes + runner.weight_bytes_per_layer())
@@ -292,22 +331,25 @@ def run_ours(args) -> None:
             "config": {"workload": WORKLOAD.replace("TP=N", f"TP={world}"), "batch": B, "ctx": ctx,
                        "layers": runner.L, "block_size": 16, "parallelism": f"tp{world}",
                        "l2": "per-step working set (KV + weights) >> 126 MB L2; kernel loop cycles 32 distinct 1 GB caches",
-                       "cuda_graph": True, "attn_splits": runner.num_splits},
+                       "cuda_graph": True, "attn_splits": runner.num_splits,
+                       "steady_state": "every timed step replays the SAME decode position (positions / seq_lens / "
+                                       "slot_mapping are not advanced: the new token's KV slot is rewritten each replay); "
+                                       "per-step work is identical to a real step at ctx 4096"},
             "tokens_per_s_per_gpu": tok_s / world,
             "e2e": {"value": B / (ms_e2e * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e},
+                    "ms_per_step": ms_e2e, "ms_per_step_device_events": ms_e2e_dev},
             "gpu_launches": runner.launches_per_step * args.steps,
             "gpu_launches_per_step": runner.launches_per_step,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "paged_decode_kernel<bf16,128,fp8_e4m3> (+combine)",
                          "achieved": achieved, "peak": pk["hbm_gbs"], "peak_kind": f"{pk_kind} copy bandwidth (burst)",
                          "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "frac_of_8TBps_nameplate": achieved / 8000.0,
-                         "traffic": NCU_ATTN_DRAM_BYTES if (world == 1 and B == 128 and ctx == 4096) else None,
-                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full, "
-                                           "profiles/r01_decode_fp8_full_v3.txt (same workload, TP1)",
+                         "traffic": traffic, "traffic_source": traffic_src,
                          "algorithmic_bytes_per_launch": attn_bytes, "ms_per_launch": attn_ms},
             "step_model": {"algorithmic_bytes_per_step": step_bytes, "hbm_frac_of_step": step_bytes / (ms_dev * 1e-3) / 1e9 / pk["hbm_gbs"]},
         }
+        if tp_check is not None:
+            line["tp_check"] = tp_check
         if world == 1 and not args.no_cpu_baseline:
             try:
                 res = cpu_sample(3, 1)
@@ -340,6 +382,7 @@ def main() -> None:
     ap.add_argument("--ctx", type=int, default=4096)
     ap.add_argument("--layers", type=int, default=None, help="debug only: fewer layers (INVALID as a bench number)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-tp-check", action="store_true")
     ap.add_argument("--profile-step", action="store_true", help="run one eager step between cudaProfilerStart/Stop")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -335,6 +335,11 @@ int b200_rotary_embedding_and_cache_write(
  *   peer_signal_pads[world_size]  device addresses of every rank's zero-initialised signal pad
  * numel 16-bit elements, multiple of 8 * world_size.  Every rank must call it in the same order.  The sum is
  * taken in rank order with fp32 accumulation: identical on all ranks and run to run.
+ *
+ * rank == -1 (all three entries): single-GPU emulation for tests on a one-GPU box.  All `world_size` buffers and
+ * signal pads live on the current device and ONE cooperative launch runs every rank (blockIdx.y = rank, so the
+ * cross-rank barriers cannot deadlock on residency).  Per-rank outputs are stacked: `out` is [world][numel];
+ * `result` / `residual` are [world][tokens][hidden] and `scales` [world][tokens].
  * ---------------------------------------------------------------------- */
 int b200_peer_all_reduce(const uint64_t* peer_buffers, const uint64_t* peer_signal_pads, int rank,
                          int world_size, int64_t numel, int dtype, int64_t byte_offset,
@@ -354,6 +359,10 @@ int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, const uint6
                                         int64_t byte_offset, int64_t signal_pad_bytes, const void* weight,
                                         void* residual, float epsilon, int64_t num_tokens, int hidden, int dtype,
                                         b200_stream_t stream);
+
+/* Spin budget of one cross-rank barrier wait, in polls (default 2^28, minutes); 0 = wait for ever.  A rank
+ * that exceeds it prints a message and traps instead of hanging the GPU. */
+void b200_peer_set_barrier_timeout(unsigned long long max_polls);
 
 /* -------------------------------------------------------------------------
  * Programmatic dependent launch (no reference counterpart).  On by default (B200_PDL=0 in the

@@ -3,6 +3,9 @@
 
   python scripts/ncu_summary.py launches gpurun_out/launches.csv        > profiles/rNN_launches.txt
   python scripts/ncu_summary.py full gpurun_out/prof_decode.ncu-rep     > profiles/rNN_decode_full.txt
+  python scripts/ncu_summary.py traffic gpurun_out/prof_decode.ncu-rep paged_decode_kernel   > profiles/attn_traffic.json
+      (per-launch dram bytes of the kernel + the digest of the kernel sources it was built from; bench.py reports
+       `roofline.traffic` from that file only while the digest still matches the tree)
 """
 import collections
 import csv
@@ -65,5 +68,41 @@ def full(path):
         print()
 
 
+def kernel_src_digest() -> str:
+    """sha256 over the attention kernel sources (same function in bench.py)."""
+    import hashlib
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parent.parent / "vllm_b200" / "csrc"
+    h = hashlib.sha256()
+    for f in ("paged_decode.cu", "paged_decode.cuh", "common.cuh"):
+        h.update((root / f).read_bytes())
+    return h.hexdigest()[:16]
+
+
+def traffic(path, pattern):
+    import json
+
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], rows[1]
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    vals = []
+    for r in rows[2:]:
+        if pattern not in r[hdr.index("Kernel Name")]:
+            continue
+        tot = 0.0
+        for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+            i = hdr.index(k)
+            tot += float(r[i].replace(",", "")) * scale.get(units[i], 1.0)
+        vals.append(tot)
+    print(json.dumps({"kernel": pattern, "launches": len(vals), "dram_bytes_per_launch": sum(vals) / max(len(vals), 1),
+                      "per_launch": vals, "source": path, "kernel_src_sha16": kernel_src_digest(),
+                      "workload": "configs[2] TP1: batch 128 x ctx 4096, fp8 KV, 32q/8kv, D=128"}))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
+    if sys.argv[1] == "traffic":
+        traffic(sys.argv[2], sys.argv[3])
+    else:
+        {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])

@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -43,9 +44,43 @@ CONFIGS = {
 }
 
 
+def patch_dummy_init() -> None:
+    """vLLM's dummy loader fills every float parameter with uniform(-1e-3, 1e-3) from the SAME seed
+    (weight_utils.py initialize_single_dummy_weight): logits come out flat, every logprob is -log(vocab) and a
+    comparison of two engines is insensitive.  Both arms therefore run with this replacement:
+    matrices ~ uniform(+-sqrt(3 / fan_in)) (variance-preserving), vectors (norm weights, biases) ~ uniform(0.5, 1.5),
+    one seed per parameter in traversal order - deterministic, identical in both arms, logits with unit spread."""
+    import torch
+    from vllm.model_executor.model_loader import dummy_loader, weight_utils
+
+    counter = [0]
+
+    @torch.no_grad()
+    def init(param, low=-1e-3, high=1e-3, seed=1234):
+        if param.device.type == "meta" or not torch.is_floating_point(param):
+            return
+        counter[0] += 1
+        g = torch.Generator(device=param.data.device)
+        g.manual_seed(seed + counter[0])
+        if param.dim() >= 2:
+            a = (3.0 / param.shape[-1]) ** 0.5
+            lo, hi = -a, a
+        else:
+            lo, hi = 0.5, 1.5
+        if torch.finfo(param.data.dtype).bits < 16:
+            param.data.copy_(param.data.to(torch.float16).uniform_(lo, hi, generator=g).to(param.data.dtype))
+        else:
+            param.uniform_(lo, hi, generator=g)
+
+    weight_utils.initialize_single_dummy_weight = init
+    dummy_loader.initialize_single_dummy_weight = init
+
+
 def worker(args) -> None:
     sys.path.insert(0, str(ROOT))
     os.environ.setdefault("VLLM_ENABLE_V1_MULTIPROCESSING", "0")
+    if not args.flat_init:
+        patch_dummy_init()
     if args.plugin:
         from vllm_b200 import plugin
 
@@ -70,13 +105,16 @@ def worker(args) -> None:
     vocab = CONFIGS[args.model]["vocab_size"]
     prompts = [{"prompt_token_ids": torch.randint(10, vocab - 10, (args.prompt_len,), generator=g).tolist()}
                for _ in range(args.num_prompts)]
-    sp = SamplingParams(temperature=0.0, max_tokens=args.decode, logprobs=1, ignore_eos=True, detokenize=False)
+    sp = SamplingParams(temperature=0.0, max_tokens=args.decode, logprobs=2, ignore_eos=True, detokenize=False)
     outs = llm.generate(prompts, sp, use_tqdm=False)
     res = []
     for o in outs:
         c = o.outputs[0]
-        lps = [float(next(iter(lp.values())).logprob) for lp in c.logprobs]
-        res.append({"tokens": list(c.token_ids), "logprobs": lps})
+        toks = list(c.token_ids)
+        # per step: logprob of the sampled token, and the top-2 {token: logprob} (to judge near-ties at a divergence)
+        lps = [float(lp[t].logprob) for lp, t in zip(c.logprobs, toks)]
+        top = [{int(k): float(v.logprob) for k, v in lp.items()} for lp in c.logprobs]
+        res.append({"tokens": toks, "logprobs": lps, "top": top})
     sel = {}
     try:
         import vllm_b200._lib as L
@@ -98,6 +136,7 @@ def main() -> None:
     ap.add_argument("--decode", type=int, default=128)
     ap.add_argument("--max-len", type=int, default=1024)
     ap.add_argument("--timeout", type=int, default=900)
+    ap.add_argument("--flat-init", action="store_true", help="keep vLLM's +-1e-3 dummy weights (flat logits)")
     ap.add_argument("--worker", action="store_true")
     ap.add_argument("--plugin", action="store_true")
     ap.add_argument("--dir")
@@ -114,7 +153,7 @@ def main() -> None:
         cmd = [sys.executable, __file__, "--worker", "--model", args.model, "--dir", str(tmp), "--out", str(out),
                "--num-prompts", str(args.num_prompts), "--prompt-len", str(args.prompt_len), "--decode", str(args.decode),
                "--max-len", str(args.max_len)] + (["--plugin"] if plug else []) + (["--fp8"] if args.fp8 else []) + (
-                   ["--eager"] if args.eager else [])
+                   ["--eager"] if args.eager else []) + (["--flat-init"] if args.flat_init else [])
         env = dict(os.environ, PYTHONPATH=f"{ROOT}:{os.environ.get('PYTHONPATH', '')}")
         r = subprocess.run(cmd, env=env, timeout=args.timeout, capture_output=True, text=True)
         if r.returncode != 0 or not out.exists():
@@ -127,11 +166,30 @@ def main() -> None:
     first_div = [next((i for i, (t1, t2) in enumerate(zip(x["tokens"], y["tokens"])) if t1 != t2), len(x["tokens"]))
                  for x, y in zip(a, b)]
     # logprob agreement on the common prefix (before any divergence the two engines saw identical contexts)
-    dl = [abs(l1 - l2) for x, y, fd in zip(a, b, first_div) for l1, l2 in zip(x["logprobs"][: fd + 1], y["logprobs"][: fd + 1])]
-    rep = {"ok": True, "model": args.model, "fp8": args.fp8, "tokens": n_tok, "tokens_equal": same,
+    dl = [abs(l1 - l2) for x, y, fd in zip(a, b, first_div) for l1, l2 in zip(x["logprobs"][:fd], y["logprobs"][:fd])]
+    # at a stream's first divergent step both engines still saw the same context: the step is a legitimate
+    # near-tie iff each engine ranks the other's choice second and within `gap` of its own
+    gaps, not_in_top2 = [], 0
+    for x, y, fd in zip(a, b, first_div):
+        if fd == len(x["tokens"]):
+            continue
+        ta, tb = x["tokens"][fd], y["tokens"][fd]
+        for top, mine, other in ((x["top"][fd], ta, tb), (y["top"][fd], tb, ta)):
+            top = {int(k): v for k, v in top.items()}
+            if other in top and mine in top:
+                gaps.append(abs(top[mine] - top[other]))
+            else:
+                not_in_top2 += 1
+    spread = [abs(l) for x in a for l in x["logprobs"]]
+    rep = {"ok": True, "model": args.model, "fp8": args.fp8, "eager": args.eager, "flat_init": args.flat_init,
+           "tokens": n_tok, "tokens_equal": same,
            "streams_identical": sum(int(fd == len(x["tokens"])) for x, fd in zip(a, first_div)), "streams": len(a),
+           "common_prefix_tokens": len(dl),
            "max_abs_logprob_diff_common_prefix": max(dl) if dl else None,
            "mean_abs_logprob_diff_common_prefix": sum(dl) / len(dl) if dl else None,
+           "divergences": sum(int(fd < len(x["tokens"])) for x, fd in zip(a, first_div)),
+           "divergence_max_top2_gap": max(gaps) if gaps else None, "divergence_other_not_in_top2": not_in_top2,
+           "mean_abs_logprob_stock": sum(spread) / len(spread), "flat_logprob_would_be": math.log(CONFIGS[args.model]["vocab_size"]),
            "b200": runs["b200"]["sel"], "stock": runs["stock"]["sel"]}
     print(json.dumps(rep))
 

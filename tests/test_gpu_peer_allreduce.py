@@ -1,4 +1,15 @@
-"""b200_peer_all_reduce / b200_peer_all_reduce_out against NCCL on two GPUs (skipped on a single-GPU box)."""
+"""b200_peer_all_reduce / _out / _rms_norm_quant.
+
+Two ways, both through the C ABI:
+  * single-GPU emulation (rank = -1, include/b200_vllm.h): all N ranks' buffers on one device, ONE cooperative
+    launch with blockIdx.y = rank.  Runs on a one-GPU box, so the two-shot kernel at 8 ranks and the fused
+    all-reduce + RMSNorm + quant at 4 ranks are checked wherever the GPU tests run;
+  * real ranks (one process per GPU, torch symmetric memory) for world in {2, 4, 8}; skipped when the box has
+    fewer GPUs.
+The expected value is the fp32 sum of the bf16 inputs rounded once (the kernels add in rank order with fp32
+accumulation), so the comparison is exact.
+"""
+import ctypes as C
 import os
 import socket
 import sys
@@ -15,12 +26,91 @@ if str(ROOT) not in sys.path:
 
 pytestmark = pytest.mark.gpu
 
+PAD_BYTES = 64 * 32 * 4  # 64 CTAs x 32 words
 
+
+def _emu_tables(world, numel, dev):
+    bufs = [torch.zeros(2 * numel, dtype=torch.bfloat16, device=dev) for _ in range(world)]
+    pads = [torch.zeros(PAD_BYTES // 4, dtype=torch.int32, device=dev) for _ in range(world)]
+    tb = (C.c_uint64 * world)(*[b.data_ptr() for b in bufs])
+    tp = (C.c_uint64 * world)(*[p.data_ptr() for p in pads])
+    return bufs, pads, tb, tp
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_emulated_all_reduce_two_shot_and_one_shot(cuda_lib, world):
+    from vllm_b200 import _lib
+
+    dev = torch.device("cuda", 0)
+    B, H = 48, 1024
+    numel = B * H
+    bufs, pads, tb, tp = _emu_tables(world, numel, dev)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    g = torch.Generator(device=dev).manual_seed(11)
+    for it in range(6):
+        idx = it & 1
+        xs = [torch.randn(B, H, device=dev, generator=g).to(torch.bfloat16) for _ in range(world)]
+        ref = torch.stack([x.float() for x in xs]).sum(0).to(torch.bfloat16)
+        for b, x in zip(bufs, xs):
+            b[idx * numel:(idx + 1) * numel].copy_(x.reshape(-1))
+        if it % 3 == 2:  # two-shot, in place
+            rc = cuda_lib.b200_peer_all_reduce(tb, tp, -1, world, numel, 2, idx * numel * 2, PAD_BYTES, st)
+            _lib.check(rc, "peer_all_reduce(emu)")
+            torch.cuda.synchronize()
+            for b in bufs:
+                assert torch.equal(b[idx * numel:(idx + 1) * numel].view(B, H), ref)
+        else:  # one-shot into per-rank outputs
+            out = torch.empty(world, B, H, dtype=torch.bfloat16, device=dev)
+            rc = cuda_lib.b200_peer_all_reduce_out(out.data_ptr(), tb, tp, -1, world, numel, 2, idx * numel * 2,
+                                                   PAD_BYTES, st)
+            _lib.check(rc, "peer_all_reduce_out(emu)")
+            torch.cuda.synchronize()
+            for r in range(world):
+                assert torch.equal(out[r], ref)
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_emulated_all_reduce_rms_norm_quant(cuda_lib, world):
+    """Fused all-reduce + residual add + RMSNorm + per-token FP8 quant == the separate kernels, bit for bit."""
+    from vllm_b200 import _lib, ops
+
+    dev = torch.device("cuda", 0)
+    B, H = 40, 2048
+    numel = B * H
+    bufs, pads, tb, tp = _emu_tables(world, numel, dev)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    g = torch.Generator(device=dev).manual_seed(5)
+    w = (torch.rand(H, device=dev, generator=g) + 0.5).to(torch.bfloat16)
+    for it in range(4):
+        idx = it & 1
+        xs = [torch.randn(B, H, device=dev, generator=g).to(torch.bfloat16) for _ in range(world)]
+        res = torch.randn(B, H, device=dev, generator=g).to(torch.bfloat16)
+        summed = torch.stack([x.float() for x in xs]).sum(0).to(torch.bfloat16)
+        res_ref = res.clone()
+        xq_ref, xs_ref = ops.rms_norm_dynamic_per_token_quant(summed, w, 1e-5, residual=res_ref)
+        for b, x in zip(bufs, xs):
+            b[idx * numel:(idx + 1) * numel].copy_(x.reshape(-1))
+        xq = torch.empty(world, B, H, dtype=torch.float8_e4m3fn, device=dev)
+        sc = torch.empty(world, B, dtype=torch.float32, device=dev)
+        resid = res.unsqueeze(0).repeat(world, 1, 1).contiguous()
+        rc = cuda_lib.b200_peer_all_reduce_rms_norm_quant(xq.data_ptr(), sc.data_ptr(), tb, tp, -1, world,
+                                                          idx * numel * 2, PAD_BYTES, w.data_ptr(), resid.data_ptr(),
+                                                          1e-5, B, H, 2, st)
+        _lib.check(rc, "peer_all_reduce_rms_norm_quant(emu)")
+        torch.cuda.synchronize()
+        for r in range(world):
+            assert torch.equal(xq[r].view(torch.uint8), xq_ref.view(torch.uint8))
+            assert torch.equal(sc[r], xs_ref.reshape(-1))
+            assert torch.equal(resid[r], res_ref)
+
+
+# ------------------------------------------------------------------------------- real ranks
 def _worker(rank, world, port, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from vllm_b200 import ops
     from vllm_b200.peer_comm import PeerAllReduce
 
     B, H = 48, 1024
@@ -38,13 +128,13 @@ def _worker(rank, world, port, q):
         else:
             got = par.all_reduce_out(it & 1, torch.empty(B, H, device=dev, dtype=torch.bfloat16))
         torch.cuda.synchronize()
-        ok = ok and torch.equal(got, ref.to(torch.bfloat16))  # fp32 accumulation, one final rounding: exact
+        # fp32 accumulation + one final rounding.  NCCL's fp32 sum order may differ from rank order by an ulp
+        # of fp32, which can flip a bf16 rounding at most in isolated elements: compare within 1 bf16 ulp and
+        # require exact agreement BETWEEN the ranks (the property the decode step relies on).
+        ok = ok and torch.allclose(got.float(), ref, rtol=8e-3, atol=1e-6)
         allg = [torch.empty_like(got) for _ in range(world)]
         dist.all_gather(allg, got.contiguous())
-        ok = ok and all(torch.equal(allg[0], t) for t in allg)  # identical on every rank
-    # fused all-reduce + residual add + RMSNorm + per-token FP8 quant == the two separate kernels, bit for bit
-    from vllm_b200 import ops
-
+        ok = ok and all(torch.equal(allg[0], t) for t in allg)
     w = (torch.rand(H, device=dev, generator=g) + 0.5).to(torch.bfloat16)
     dist.broadcast(w, 0)
     for it in range(4):
@@ -68,14 +158,16 @@ def _worker(rank, world, port, q):
     os._exit(0)
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_peer_all_reduce_matches_fp32_sum():
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_peer_all_reduce_real_ranks(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
     assert q.get(timeout=300)

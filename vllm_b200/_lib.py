@@ -70,6 +70,7 @@ SIGNATURES: dict[str, tuple] = {
     "b200_peer_all_reduce": (i32, [vp, vp, i32, i32, i64, i32, i64, i64, vp]),
     "b200_peer_all_reduce_out": (i32, [vp, vp, vp, i32, i32, i64, i32, i64, i64, vp]),
     "b200_peer_all_reduce_rms_norm_quant": (i32, [vp, vp, vp, vp, i32, i32, i64, i64, vp, vp, f32, i64, i32, i32, vp]),
+    "b200_peer_set_barrier_timeout": (None, [C.c_ulonglong]),
     "b200_set_pdl": (None, [i32]),
     "b200_get_pdl": (i32, []),
     "b200_debug_gemm_trace": (None, [vp]),

@@ -139,6 +139,9 @@ class B200AttentionMetadataBuilder(AttentionMetadataBuilder[B200AttentionMetadat
             req = torch.searchsorted(qsl[1:].contiguous(), tok, right=True).clamp_(max=m.seq_lens.shape[0] - 1)
             self._token_to_seq[:T].copy_(req)
             lens = m.seq_lens[req] - (qsl[1:][req] - 1 - tok)
+            # CUDA-graph pad tokens (tok >= query_start_loc[-1]) belong to no request: length 0, so the kernel
+            # writes zeros for them and never walks block_table entries past the last request's blocks
+            lens = torch.where(tok < qsl[-1], lens, torch.zeros_like(lens))
             self._token_seq_lens[:T].copy_(lens.clamp_(min=0))
             md.token_to_seq = self._token_to_seq[:T]
             md.token_seq_lens = self._token_seq_lens[:T]

@@ -34,6 +34,9 @@ void count_launch(int n = 1);
   } while (0)
 
 int sm_count();
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-device (per-context) property of a kernel: remembered
+// per (kernel, device) so a process that drives several GPUs opts in on each of them.  Returns a B200_* code.
+int ensure_dyn_smem(const void* kernel, int bytes);
 
 // ---- launch helper: programmatic dependent launch (PDL) ---------------------------------------
 // Every kernel of this library is launched with the programmatic-stream-serialization attribute, so the
@@ -45,14 +48,14 @@ int sm_count();
 bool pdl_enabled();
 
 template <typename... KArgs, typename... Args>
-inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
-                                 int cluster_x, Args&&... args) {
+inline cudaError_t launch_kernel_ex(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                    int cluster_x, bool cooperative, Args&&... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute at[2];
+  cudaLaunchAttribute at[3];
   int n = 0;
   if (cluster_x > 1) {
     at[n].id = cudaLaunchAttributeClusterDimension;
@@ -61,7 +64,11 @@ inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, 
     at[n].val.clusterDim.z = 1;
     ++n;
   }
-  if (pdl_enabled()) {
+  if (cooperative) {  // all CTAs co-resident or the launch fails (single-GPU emulation of cross-rank barriers)
+    at[n].id = cudaLaunchAttributeCooperative;
+    at[n].val.cooperative = 1;
+    ++n;
+  } else if (pdl_enabled()) {
     at[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[n].val.programmaticStreamSerializationAllowed = 1;
     ++n;
@@ -69,6 +76,11 @@ inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, 
   cfg.attrs = at;
   cfg.numAttrs = n;
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                 int cluster_x, Args&&... args) {
+  return launch_kernel_ex(kern, grid, block, smem, stream, cluster_x, false, static_cast<Args&&>(args)...);
 }
 
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

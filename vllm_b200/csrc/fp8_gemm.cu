@@ -8,14 +8,9 @@
 //   warp 0   TMA producer   (X tile 128 x 128B, Y tile BN x 128B per stage, SW128)
 //   warp 1   TMEM alloc + single-thread tcgen05.mma.kind::f8f6f4 issue (4 x K32 per stage)
 //   warps 2-5 epilogue      (tcgen05.ld 32x32b, scales, bias, cast, store)
-// Decode regime (M <= 256, weight-bandwidth bound): fp8_gemm_decode_kernel below -- swap-AB
-// (128 weight rows per tile on the UMMA-M axis, tokens on UMMA-N = 16..256), PERSISTENT
-// one CTA per SM, stream-K: the (tile, k-block) units are cut into 148 equal contiguous
-// ranges so every SM streams the same number of weight bytes whatever N is; two TMEM
-// accumulators so the epilogue of one segment overlaps the TMA/MMA stream of the next;
-// a tile whose K range spans several CTAs is fixed up through an fp32 workspace (the tail
-// owners emit partials as their FIRST segment, the head owner adds them in its LAST).
-// Large M: tokens on X, weights on Y, BN = 256 (fp8_gemm_kernel).
+// This file: the one-tile-per-CTA kernel (tokens on X, weights on Y, BN = 128/256) and the C entry point.
+// The decode regime (M <= 256, weight-bandwidth bound) lives in fp8_gemm_decode.cu; large M goes to the
+// persistent 2-CTA kernel in gemm_persist.cu when the shape allows, else to the kernel below.
 #include <cuda.h>
 
 #include <mutex>
@@ -45,12 +40,9 @@ struct GemmArgs {
   const float* a_scales;  // per token (M) or [1]
   const float* b_scales;  // per channel (N) or [1]
   const void* bias;       // [N] out dtype or null
-  float* splitk_ws;       // fp32 [M][N] zero-initialised (split-K only)
-  int* splitk_cnt;        // per output tile arrival counters, zero-initialised
   int64_t ldc;
   int M, N, K;
   int a_scales_numel, b_scales_numel;
-  int k_blocks_per_split;
 };
 
 template <typename OutT> __device__ __forceinline__ void store16(OutT* dst, const float (&v)[16], bool vec_ok);
@@ -102,10 +94,8 @@ __global__ void __launch_bounds__(kGemmThreads, kTwo ? 2 : 1)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int x0 = blockIdx.x * 128, y0 = blockIdx.y * BN;
-  const int total_kb = (g.K + kBK - 1) / kBK;
-  const int kb_begin = blockIdx.z * g.k_blocks_per_split;
-  const int kb_end = min(total_kb, kb_begin + g.k_blocks_per_split);
-  const int nkb = kb_end - kb_begin;  // host guarantees > 0
+  const int nkb = (g.K + kBK - 1) / kBK;
+  const int kb_begin = 0, kb_end = nkb;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -179,7 +169,6 @@ __global__ void __launch_bounds__(kGemmThreads, kTwo ? 2 : 1)
     const int y_lim = kSwap ? g.M : g.N;
     OutT* outp = reinterpret_cast<OutT*>(g.out);
     const OutT* bias = reinterpret_cast<const OutT*>(g.bias);
-    const bool split = gridDim.z > 1;
     // per-row (X side) scale and bias
     float sx_row = 1.f, bias_row = 0.f;
     if (xi < x_lim) {
@@ -196,18 +185,6 @@ __global__ void __launch_bounds__(kGemmThreads, kTwo ? 2 : 1)
       umma::ld_32x32b_x16(tmem_base + ((uint32_t)(q * 32) << 16) + c, r);
       umma::ld_wait();
       if (xi >= x_lim || y0 + c >= y_lim) continue;
-      if (split) {
-        // accumulate raw fp32 partials; scaling happens in the finishing pass
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int yj = y0 + c + j;
-          if (yj < y_lim) {
-            const int64_t o = kSwap ? (int64_t)yj * g.N + xi : (int64_t)xi * g.N + yj;
-            atomicAdd(g.splitk_ws + o, __uint_as_float(r[j]));
-          }
-        }
-        continue;
-      }
       float v[16];
       if constexpr (kSwap) {
 #pragma unroll
@@ -227,35 +204,6 @@ __global__ void __launch_bounds__(kGemmThreads, kTwo ? 2 : 1)
         }
         OutT* dst = outp + (int64_t)xi * g.ldc + y0 + c;
         store16<OutT>(dst, v, (reinterpret_cast<uintptr_t>(dst) & 15) == 0);
-      }
-    }
-    if (split) {
-      // last CTA of this output tile converts the accumulated workspace and re-zeroes it
-      __threadfence();
-      asm volatile("bar.sync 1, 128;" ::: "memory");  // epilogue warps only
-      __shared__ int s_last;
-      if (threadIdx.x == 64) {
-        const int tile = blockIdx.y * gridDim.x + blockIdx.x;
-        const int prev = atomicAdd(g.splitk_cnt + tile, 1);
-        s_last = (prev == (int)gridDim.z - 1);
-        if (s_last) g.splitk_cnt[tile] = 0;
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (s_last) {
-        __threadfence();
-        if (xi < x_lim) {
-          for (int j = 0; j < BN; ++j) {
-            const int yj = y0 + j;
-            if (yj >= y_lim) break;
-            const int m = kSwap ? yj : xi, n = kSwap ? xi : yj;
-            float* w = g.splitk_ws + (int64_t)m * g.N + n;
-            const float acc = __ldcg(w);
-            *w = 0.f;
-            const float as = g.a_scales[g.a_scales_numel > 1 ? m : 0];
-            const float bs = g.b_scales[g.b_scales_numel > 1 ? n : 0];
-            outp[(int64_t)m * g.ldc + n] = from_float<OutT>(acc * as * bs + (bias ? to_float(bias[n]) : 0.f));
-          }
-        }
       }
     }
   }
@@ -310,15 +258,7 @@ static int launch_fp8_gemm(const CUtensorMap& tx, const CUtensorMap& ty, const G
                            cudaStream_t stream) {
   using Cfg = GemmCfg<BN, kTwo>;
   auto kern = fp8_gemm_kernel<BN, kSwap, OutT, kTwo>;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (e != cudaSuccess) {
-      set_error("fp8 gemm: cudaFuncSetAttribute(%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
-      return B200_ERR_CUDA;
-    }
-    attr = true;
-  }
+  if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES)) return rc_attr;
   launch_kernel(kern, dim3(grid), dim3(kGemmThreads), Cfg::SMEM_BYTES, stream, 1, tx, ty, g);
   B200_CHECK_LAUNCH();
   count_launch();
@@ -347,10 +287,6 @@ static int run_fp8_gemm(void* out, const void* a, const void* b, const float* a_
   g.K = K;
   g.a_scales_numel = a_scales_numel;
   g.b_scales_numel = b_scales_numel;
-  g.splitk_ws = nullptr;
-  g.splitk_cnt = nullptr;
-  const int total_kb = (K + kBK - 1) / kBK;
-  g.k_blocks_per_split = total_kb;
   if (M <= 256)
     return run_fp8_decode<OutT>(out, a, b, a_scales, b_scales, bias, M, N, K, lda, ldb, ldc, a_scales_numel,
                                 b_scales_numel, workspace, workspace_bytes, stream);

@@ -642,15 +642,7 @@ static int launch_fp8_decode(const CUtensorMap& tw, const CUtensorMap& ta, const
                              int cluster_size, cudaStream_t stream, int* max_active_out = nullptr) {
   using Cfg = DecCfg<BN>;
   auto kern = fp8_gemm_decode_kernel<BN, OutT>;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (e != cudaSuccess) {
-      set_error("fp8 decode gemm: cudaFuncSetAttribute(%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
-      return B200_ERR_CUDA;
-    }
-    attr = true;
-  }
+  if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES)) return rc_attr;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(cluster_size * num_clusters, 1, 1);
   cfg.blockDim = dim3(kDecThreads, 1, 1);

@@ -145,8 +145,8 @@ __global__ void __launch_bounds__(1024) rms_norm_quant_kernel(uint8_t* __restric
 // alternates between two buffers (see b200_peer_all_reduce_out).
 template <typename T>
 __global__ void __launch_bounds__(1024) peer_allreduce_rms_norm_quant_kernel(
-    uint8_t* __restrict__ out, float* __restrict__ scales, const ArArgs a, const T* __restrict__ w,
-    T* __restrict__ residual, int num_tokens, int hidden, float eps) {
+    uint8_t* out, float* scales, const ArArgs a, const T* __restrict__ w, T* residual, int num_tokens, int hidden,
+    float eps) {
   pdl_trigger();
   pdl_wait();
   constexpr int N = 8;
@@ -155,9 +155,15 @@ __global__ void __launch_bounds__(1024) peer_allreduce_rms_norm_quant_kernel(
   extern __shared__ __align__(16) uint8_t row_buf[];
   float* rowf = reinterpret_cast<float*>(row_buf);
   if ((int)threadIdx.x < a.world) s_pads[threadIdx.x] = a.pads[threadIdx.x];
-  uint32_t* my_epoch = a.pads[a.rank] + blockIdx.x * kArSlotWords + 2 * kArMaxWorld;
+  const int rank = ar_rank(a);
+  if (a.emu) {  // single-GPU emulation: every emulated rank has its own outputs and residual
+    out += (int64_t)rank * a.emu_stride;
+    residual += (int64_t)rank * a.emu_stride;
+    scales += (int64_t)rank * num_tokens;
+  }
+  uint32_t* my_epoch = a.pads[rank] + blockIdx.x * kArSlotWords + 2 * kArMaxWorld;
   const uint32_t epoch = *my_epoch + 1;
-  ar_barrier(s_pads, a.rank, a.world, 0, epoch);
+  ar_barrier(s_pads, rank, a.world, 0, epoch, a.spin_limit);
   const int nv = hidden / N;
   for (int row = blockIdx.x; row < num_tokens; row += gridDim.x) {
     T* res = residual + (int64_t)row * hidden;
@@ -422,11 +428,7 @@ extern "C" int b200_rms_norm_dynamic_per_token_quant(void* result, const void* i
                  "rms_norm_dynamic_per_token_quant: null pointer");
   return dispatch16f(dtype, "rms_norm_dynamic_per_token_quant", [&](auto tag) {
     using T = decltype(tag);
-    static bool attr = false;
-    if (!attr) {
-      cudaFuncSetAttribute(rms_norm_quant_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 49152 * 4);
-      attr = true;
-    }
+    if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(rms_norm_quant_kernel<T>), 49152 * 4)) return rc_attr;
     const int threads = row_threads(hidden / (int)(16 / sizeof(T)));
     launch_kernel(rms_norm_quant_kernel<T>, dim3((unsigned)num_tokens), dim3(threads), hidden * 4, (cudaStream_t)stream, 1, 
         (uint8_t*)result, scales, (const T*)input, (const T*)weight, (T*)residual, scale_ub, hidden, in_row_stride,
@@ -448,11 +450,7 @@ extern "C" int b200_silu_and_mul_dynamic_per_token_quant(void* result, float* sc
                  "silu_and_mul_dynamic_per_token_quant: input must be 16-byte aligned");
   return dispatch16f(dtype, "silu_and_mul_dynamic_per_token_quant", [&](auto tag) {
     using T = decltype(tag);
-    static bool attr = false;
-    if (!attr) {
-      cudaFuncSetAttribute(silu_mul_quant_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 98304 * 2);
-      attr = true;
-    }
+    if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(silu_mul_quant_kernel<T>), 98304 * 2)) return rc_attr;
     const int threads = row_threads(d / (int)(16 / sizeof(T)));
     launch_kernel(silu_mul_quant_kernel<T>, dim3((unsigned)num_tokens), dim3(threads), d * sizeof(T), (cudaStream_t)stream, 1, 
         (uint8_t*)result, scales, (const T*)input, d);
@@ -507,7 +505,9 @@ extern "C" int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, 
   using namespace b200;
   B200_CHECK_ARG(result && scales && peer_buffers && peer_signal_pads && weight && residual, B200_ERR_INVALID_ARG,
                  "peer_all_reduce_rms_norm_quant: null pointer");
-  B200_CHECK_ARG(world_size >= 2 && world_size <= kArMaxWorld && rank >= 0 && rank < world_size, B200_ERR_INVALID_ARG,
+  const bool emu = rank == -1;  // single-GPU emulation of all ranks (see include/b200_vllm.h)
+  B200_CHECK_ARG(world_size >= 2 && world_size <= kArMaxWorld && (emu || (rank >= 0 && rank < world_size)),
+                 B200_ERR_INVALID_ARG,
                  "peer_all_reduce_rms_norm_quant: world size %d / rank %d not supported (2..8 ranks)", world_size, rank);
   B200_CHECK_ARG(num_tokens > 0 && hidden > 0 && hidden % 8 == 0 && hidden <= 49152 && byte_offset % 16 == 0,
                  B200_ERR_INVALID_ARG, "peer_all_reduce_rms_norm_quant: hidden must be a multiple of 8 (<= 49152)");
@@ -516,6 +516,7 @@ extern "C" int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, 
                  B200_ERR_ALIGNMENT, "peer_all_reduce_rms_norm_quant: weight/residual must be 16-byte aligned");
   int64_t grid = num_tokens < 64 ? num_tokens : 64;
   const int64_t max_grid = signal_pad_bytes / (kArSlotWords * 4);
+  if (emu && grid > sm_count() / world_size) grid = sm_count() / world_size;  // one cooperative wave
   if (grid > max_grid) grid = max_grid;
   B200_CHECK_ARG(grid >= 1, B200_ERR_INVALID_ARG, "peer_all_reduce_rms_norm_quant: signal pad too small");
   ArArgs a;
@@ -523,20 +524,19 @@ extern "C" int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, 
     a.bufs[q] = q < world_size ? reinterpret_cast<void*>(peer_buffers[q] + byte_offset) : nullptr;
     a.pads[q] = q < world_size ? reinterpret_cast<uint32_t*>(peer_signal_pads[q]) : nullptr;
   }
-  a.rank = rank;
+  a.rank = emu ? 0 : rank;
   a.world = world_size;
   a.numel = num_tokens * hidden;
+  a.spin_limit = ar_spin_limit();
+  a.emu = emu ? 1 : 0;
+  a.emu_stride = num_tokens * hidden;
   return dispatch16f(dtype, "peer_all_reduce_rms_norm_quant", [&](auto tag) {
     using T = decltype(tag);
-    static bool attr = false;
-    if (!attr) {
-      cudaFuncSetAttribute(peer_allreduce_rms_norm_quant_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 49152 * 4);
-      attr = true;
-    }
+    if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(peer_allreduce_rms_norm_quant_kernel<T>), 49152 * 4)) return rc_attr;
     const int threads = row_threads(hidden / 8);
-    launch_kernel(peer_allreduce_rms_norm_quant_kernel<T>, dim3((unsigned)grid), dim3(threads), hidden * 4,
-                  (cudaStream_t)stream, 1, (uint8_t*)result, scales, a, (const T*)weight, (T*)residual, (int)num_tokens,
-                  hidden, epsilon);
+    launch_kernel_ex(peer_allreduce_rms_norm_quant_kernel<T>, dim3((unsigned)grid, emu ? world_size : 1), dim3(threads),
+                     hidden * 4, (cudaStream_t)stream, 1, emu, (uint8_t*)result, scales, a, (const T*)weight,
+                     (T*)residual, (int)num_tokens, hidden, epsilon);
     B200_CHECK_LAUNCH();
     count_launch();
     return 0;

@@ -201,11 +201,7 @@ extern "C" int b200_rms_norm(void* out, const void* input, const void* weight, v
   B200_CHECK_ARG(out && input && weight, B200_ERR_INVALID_ARG, "rms_norm: null pointer");
   return dispatch16(dtype, "rms_norm", [&](auto tag) {
     using T = decltype(tag);
-    static bool attr = false;
-    if (!attr) {
-      cudaFuncSetAttribute(rms_norm_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768 * 4);
-      attr = true;
-    }
+    if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(rms_norm_kernel<T>), 32768 * 4)) return rc_attr;
     launch_kernel(rms_norm_kernel<T>, dim3((unsigned)num_tokens), dim3(256), hidden * 4, (cudaStream_t)stream, 1, 
         (T*)out, (const T*)input, (const T*)weight, (T*)residual, hidden, in_row_stride, eps);
     B200_CHECK_LAUNCH();

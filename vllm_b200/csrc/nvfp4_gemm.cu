@@ -225,15 +225,7 @@ template <int BN, bool kSwap, typename OutT>
 static int launch_f4(const CUtensorMap& tx, const CUtensorMap& ty, const F4Args& g, dim3 grid, cudaStream_t stream) {
   using Cfg = F4Cfg<BN>;
   auto kern = nvfp4_gemm_kernel<BN, kSwap, OutT>;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (e != cudaSuccess) {
-      set_error("nvfp4 gemm: cudaFuncSetAttribute(%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
-      return B200_ERR_CUDA;
-    }
-    attr = true;
-  }
+  if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES)) return rc_attr;
   launch_kernel(kern, dim3(grid), dim3(kF4Threads), Cfg::SMEM_BYTES, stream, 1, tx, ty, g);
   B200_CHECK_LAUNCH();
   count_launch();

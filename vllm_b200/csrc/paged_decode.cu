@@ -617,17 +617,9 @@ template <typename QT, int D, int KV>
 static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const DecodeArgs& a, int num_seqs,
                          cudaStream_t stream) {
   using Cfg = DecodeCfg<D, KV>;
-  static bool attr_set[2] = {false, false};
   const bool r8 = a.group <= 8;
   auto kern = r8 ? paged_decode_kernel<QT, D, KV, true> : paged_decode_kernel<QT, D, KV, false>;
-  if (!attr_set[r8]) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (e != cudaSuccess) {
-      set_error("cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
-      return B200_ERR_CUDA;
-    }
-    attr_set[r8] = true;
-  }
+  if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES)) return rc_attr;
   // fp8 caches: the register-level kernel below is the default.  The tcgen05 kernel (paged_decode_fp8.cu)
   // is parity-green but measured 5-15% slower on the BASELINE shapes (profiles/r01_attn_fp8_tcgen05.md:
   // bound by the TMA request rate for 128-byte cache rows and by the QK->softmax->PV latency chain);

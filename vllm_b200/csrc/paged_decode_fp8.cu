@@ -655,15 +655,7 @@ static int launch_fp8_nh(const CUtensorMap& tk, const CUtensorMap& tv, const Dec
                          cudaStream_t stream) {
   using Cfg = Fp8Cfg<D>;
   auto kern = paged_decode_fp8_kernel<QT, D, KV, NH>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    if (e != cudaSuccess) {
-      set_error("cudaFuncSetAttribute(smem=%d) failed: %s", Cfg::SMEM_BYTES, cudaGetErrorString(e));
-      return B200_ERR_CUDA;
-    }
-    attr_set = true;
-  }
+  if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES)) return rc_attr;
   dim3 grid(a.num_splits, a.num_kv_heads * a.qgroups, num_seqs);
   launch_kernel(kern, grid, dim3(kF8Threads), Cfg::SMEM_BYTES, stream, 1, tk, tv, a);
   B200_CHECK_LAUNCH();

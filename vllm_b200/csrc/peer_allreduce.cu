@@ -18,6 +18,8 @@
 //   barrier            all stores have landed: the local consumer may read the whole buffer
 // CTA b of every rank only ever synchronises with CTA b of the other ranks (signal-pad slots [b][peer]), so the
 // grid never needs more co-residency than "the same CTA index is running on every GPU".
+#include <atomic>
+
 #include "peer_sync.cuh"
 
 namespace b200 {
@@ -29,13 +31,14 @@ __global__ void __launch_bounds__(kArThreads) peer_all_reduce_kernel(const ArArg
   pdl_wait();  // the producer of the local buffer has finished
   __shared__ uint32_t* s_pads[kArMaxWorld];
   if ((int)threadIdx.x < a.world) s_pads[threadIdx.x] = a.pads[threadIdx.x];
-  uint32_t* my_epoch = a.pads[a.rank] + blockIdx.x * kArSlotWords + 2 * kArMaxWorld;
+  const int rank = ar_rank(a);
+  uint32_t* my_epoch = a.pads[rank] + blockIdx.x * kArSlotWords + 2 * kArMaxWorld;
   const uint32_t epoch = *my_epoch + 1;  // every rank runs the same sequence of calls: the epochs agree
-  ar_barrier(s_pads, a.rank, a.world, 0, epoch);
+  ar_barrier(s_pads, rank, a.world, 0, epoch, a.spin_limit);
 
   const int64_t vec_total = a.numel / 8;            // 16-byte vectors
   const int64_t per_rank = vec_total / a.world;     // my slice
-  const int64_t v0 = per_rank * a.rank;
+  const int64_t v0 = per_rank * rank;
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < per_rank; v += (int64_t)gridDim.x * blockDim.x) {
     float acc[8];
 #pragma unroll
@@ -59,7 +62,7 @@ __global__ void __launch_bounds__(kArThreads) peer_all_reduce_kernel(const ArArg
     for (int q = 0; q < kArMaxWorld; ++q)
       if (q < a.world) reinterpret_cast<uint4*>(a.bufs[q])[v0 + v] = o;
   }
-  ar_barrier(s_pads, a.rank, a.world, 1, epoch);
+  ar_barrier(s_pads, rank, a.world, 1, epoch, a.spin_limit);
   if (threadIdx.x == 0) *my_epoch = epoch;
 }
 
@@ -68,14 +71,16 @@ __global__ void __launch_bounds__(kArThreads) peer_all_reduce_kernel(const ArArg
 // buffer X (two calls later) only after passing the start barrier of the call in between, which every peer
 // reaches only after it has finished reading X.
 template <typename T>
-__global__ void __launch_bounds__(kArThreads) peer_all_reduce_oneshot_kernel(const ArArgs a, T* __restrict__ out) {
+__global__ void __launch_bounds__(kArThreads) peer_all_reduce_oneshot_kernel(const ArArgs a, T* out) {
   pdl_trigger();
   pdl_wait();
   __shared__ uint32_t* s_pads[kArMaxWorld];
   if ((int)threadIdx.x < a.world) s_pads[threadIdx.x] = a.pads[threadIdx.x];
-  uint32_t* my_epoch = a.pads[a.rank] + blockIdx.x * kArSlotWords + 2 * kArMaxWorld;
+  const int rank = ar_rank(a);
+  if (a.emu) out += rank * a.emu_stride;
+  uint32_t* my_epoch = a.pads[rank] + blockIdx.x * kArSlotWords + 2 * kArMaxWorld;
   const uint32_t epoch = *my_epoch + 1;
-  ar_barrier(s_pads, a.rank, a.world, 0, epoch);
+  ar_barrier(s_pads, rank, a.world, 0, epoch, a.spin_limit);
   const int64_t vec_total = a.numel / 8;
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < vec_total; v += (int64_t)gridDim.x * blockDim.x) {
     uint4 in[kArMaxWorld];
@@ -104,13 +109,24 @@ __global__ void __launch_bounds__(kArThreads) peer_all_reduce_oneshot_kernel(con
 
 }  // namespace b200
 
+namespace b200 {
+static std::atomic<unsigned long long> g_ar_spin_limit{1ull << 28};
+unsigned long long ar_spin_limit() { return g_ar_spin_limit.load(std::memory_order_relaxed); }
+}  // namespace b200
+
+extern "C" void b200_peer_set_barrier_timeout(unsigned long long max_polls) {
+  b200::g_ar_spin_limit.store(max_polls, std::memory_order_relaxed);
+}
+
 static int peer_all_reduce_impl(void* out, const uint64_t* peer_buffers, const uint64_t* peer_signal_pads, int rank,
                                 int world_size, int64_t numel, int dtype, int64_t byte_offset,
                                 int64_t signal_pad_bytes, b200_stream_t stream) {
   using namespace b200;
   B200_CHECK_ARG(peer_buffers && peer_signal_pads, B200_ERR_INVALID_ARG, "peer_all_reduce: null pointer table");
-  B200_CHECK_ARG(world_size >= 2 && world_size <= kArMaxWorld && rank >= 0 && rank < world_size, B200_ERR_INVALID_ARG,
-                 "peer_all_reduce: world size %d / rank %d not supported (2..8 ranks)", world_size, rank);
+  const bool emu = rank == -1;  // single-GPU emulation of all ranks (see include/b200_vllm.h)
+  B200_CHECK_ARG(world_size >= 2 && world_size <= kArMaxWorld && (emu || (rank >= 0 && rank < world_size)),
+                 B200_ERR_INVALID_ARG, "peer_all_reduce: world size %d / rank %d not supported (2..8 ranks)", world_size,
+                 rank);
   B200_CHECK_ARG(dtype == B200_DT_BF16 || dtype == B200_DT_F16, B200_ERR_UNSUPPORTED,
                  "peer_all_reduce: only 16-bit floating point tensors");
   B200_CHECK_ARG(numel > 0 && numel % (8 * world_size) == 0 && byte_offset % 16 == 0, B200_ERR_INVALID_ARG,
@@ -121,6 +137,7 @@ static int peer_all_reduce_impl(void* out, const uint64_t* peer_buffers, const u
   int grid = (int)((per_rank_vec + kArThreads - 1) / kArThreads);
   const int64_t max_grid = signal_pad_bytes / (kArSlotWords * 4);
   if (grid > 64) grid = 64;
+  if (emu && grid > sm_count() / world_size) grid = sm_count() / world_size;  // one cooperative wave
   if (grid > max_grid) grid = (int)max_grid;
   B200_CHECK_ARG(grid >= 1, B200_ERR_INVALID_ARG, "peer_all_reduce: signal pad too small (%lld bytes)",
                  (long long)signal_pad_bytes);
@@ -129,22 +146,26 @@ static int peer_all_reduce_impl(void* out, const uint64_t* peer_buffers, const u
     a.bufs[q] = q < world_size ? reinterpret_cast<void*>(peer_buffers[q] + byte_offset) : nullptr;
     a.pads[q] = q < world_size ? reinterpret_cast<uint32_t*>(peer_signal_pads[q]) : nullptr;
   }
-  a.rank = rank;
+  a.rank = emu ? 0 : rank;
   a.world = world_size;
   a.numel = numel;
+  a.spin_limit = ar_spin_limit();
+  a.emu = emu ? 1 : 0;
+  a.emu_stride = numel;
   cudaStream_t s = (cudaStream_t)stream;
+  const dim3 g(grid, emu ? world_size : 1);
   if (out) {
     B200_CHECK_ARG(reinterpret_cast<uintptr_t>(out) % 16 == 0, B200_ERR_ALIGNMENT, "peer_all_reduce: out must be 16-byte aligned");
     if (dtype == B200_DT_BF16)
-      launch_kernel(peer_all_reduce_oneshot_kernel<__nv_bfloat16>, dim3(grid), dim3(kArThreads), 0, s, 1, a,
-                    reinterpret_cast<__nv_bfloat16*>(out));
+      launch_kernel_ex(peer_all_reduce_oneshot_kernel<__nv_bfloat16>, g, dim3(kArThreads), 0, s, 1, emu, a,
+                       reinterpret_cast<__nv_bfloat16*>(out));
     else
-      launch_kernel(peer_all_reduce_oneshot_kernel<__half>, dim3(grid), dim3(kArThreads), 0, s, 1, a,
-                    reinterpret_cast<__half*>(out));
+      launch_kernel_ex(peer_all_reduce_oneshot_kernel<__half>, g, dim3(kArThreads), 0, s, 1, emu, a,
+                       reinterpret_cast<__half*>(out));
   } else if (dtype == B200_DT_BF16) {
-    launch_kernel(peer_all_reduce_kernel<__nv_bfloat16>, dim3(grid), dim3(kArThreads), 0, s, 1, a);
+    launch_kernel_ex(peer_all_reduce_kernel<__nv_bfloat16>, g, dim3(kArThreads), 0, s, 1, emu, a);
   } else {
-    launch_kernel(peer_all_reduce_kernel<__half>, dim3(grid), dim3(kArThreads), 0, s, 1, a);
+    launch_kernel_ex(peer_all_reduce_kernel<__half>, g, dim3(kArThreads), 0, s, 1, emu, a);
   }
   B200_CHECK_LAUNCH();
   count_launch();

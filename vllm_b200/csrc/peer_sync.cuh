@@ -19,19 +19,26 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   return v;
 }
 constexpr int kArSlotWords = 32;
+// Spin budget of one barrier wait, host-configurable (b200_peer_set_barrier_timeout): 0 = wait for ever.  The
+// default (~2^28 polls, minutes) only exists so that a protocol bug or a dead peer ends in a trap with a message
+// instead of a GPU that has to be reset; legitimately skewed ranks (one still capturing a graph) fit well inside it.
+unsigned long long ar_spin_limit();  // host: current budget, copied into ArArgs::spin_limit at launch
 // all ranks' CTA `blockIdx.x` meet: thread t < world signals rank t and waits for rank t's signal.  The
 // bar.sync before the release store makes every thread's earlier (peer) stores part of what is released.
-__device__ __forceinline__ void ar_barrier(uint32_t* const* pads, int rank, int world, int phase, uint32_t epoch) {
+// Epochs only grow, and the wait is a wraparound-safe ">= epoch": the one-shot kernels have no end barrier, so
+// a fast peer may already have stored epoch n+1 into this slot before a stalled waiter polls for n.
+__device__ __forceinline__ void ar_barrier(uint32_t* const* pads, int rank, int world, int phase, uint32_t epoch,
+                                           unsigned long long limit) {
   __syncthreads();
   if ((int)threadIdx.x < world) {
     const int slot = blockIdx.x * kArSlotWords + phase * kArMaxWorld;
     st_release_sys(pads[threadIdx.x] + slot + rank, epoch);  // my flag in the peer's pad
     const uint32_t* mine = pads[rank] + slot + threadIdx.x;  // the peer's flag in my pad
-    uint32_t spins = 0;
-    while (ld_acquire_sys(mine) != epoch) {
-      if (++spins > (1u << 24)) {
-        printf("b200: peer all-reduce barrier timed out (block %d waits for rank %d, phase %d)\n", blockIdx.x,
-               threadIdx.x, phase);
+    unsigned long long spins = 0;
+    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+      if (limit && ++spins > limit) {
+        printf("b200: peer all-reduce barrier timed out (block %d waits for rank %d, phase %d, epoch %u)\n",
+               blockIdx.x, threadIdx.x, phase, epoch);
         __trap();
       }
     }
@@ -39,11 +46,22 @@ __device__ __forceinline__ void ar_barrier(uint32_t* const* pads, int rank, int 
   __syncthreads();
 }
 
+struct ArArgs;
+__device__ __forceinline__ int ar_rank(const ArArgs& a);
+
 struct ArArgs {
   void* bufs[kArMaxWorld];
   uint32_t* pads[kArMaxWorld];
   int rank, world;
   int64_t numel;  // 16-bit elements, multiple of 8 * world
+  unsigned long long spin_limit;  // barrier spin budget, 0 = unbounded
+  // Single-GPU emulation of `world` ranks (tests on a 1-GPU box): ONE cooperative launch with gridDim.y = world,
+  // rank = blockIdx.y, every "rank's" buffer / signal pad on the same device; per-rank outputs are `emu_stride`
+  // elements apart.  0 in production.
+  int emu;
+  int64_t emu_stride;
 };
+
+__device__ __forceinline__ int ar_rank(const ArArgs& a) { return a.emu ? (int)blockIdx.y : a.rank; }
 
 }  // namespace b200

@@ -9,6 +9,8 @@
 
 #include <atomic>
 #include <mutex>
+#include <utility>
+#include <vector>
 
 #include "common.cuh"
 
@@ -48,6 +50,24 @@ int sm_count() {
     cached[dev] = n;
   }
   return cached[dev];
+}
+
+int ensure_dyn_smem(const void* kernel, int bytes) {
+  static std::mutex mu;
+  static std::vector<std::pair<const void*, int>> done;  // (kernel, device) pairs already opted in
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+  std::lock_guard<std::mutex> lk(mu);
+  for (const auto& p : done)
+    if (p.first == kernel && p.second == dev) return 0;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) {
+    set_error("cudaFuncSetAttribute(MaxDynamicSharedMemorySize=%d) failed on device %d: %s", bytes, dev,
+              cudaGetErrorString(e));
+    return B200_ERR_CUDA;
+  }
+  done.emplace_back(kernel, dev);
+  return 0;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,

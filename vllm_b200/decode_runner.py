@@ -27,7 +27,7 @@ import sys
 import torch
 import torch.distributed as dist
 
-from . import _lib, ops
+from . import _lib, ops, tp_shard
 
 
 @dataclasses.dataclass
@@ -69,29 +69,40 @@ class DecodeRunner:
         self.inter = shape.intermediate // tp_size
         self.vocab_shard = (shape.vocab + tp_size - 1) // tp_size
         self.dtype = torch.bfloat16
+        # ONE seeded full model, identical on every rank, sharded the way vLLM's parallel linears shard a
+        # checkpoint (tp_shard.py): TP=N computes the same function as TP=1 up to the quantisation / summation
+        # order noise of the row-parallel all-reduce (tests/test_gpu_tp_equivalence.py, bench.py "tp_check").
         g = torch.Generator(device=self.dev)
-        g.manual_seed(seed * 1000 + tp_rank)
-        gshared = torch.Generator(device=self.dev)
-        gshared.manual_seed(seed)  # tensors that must be identical on every rank
+        g.manual_seed(seed)
         H = shape.hidden
+        lay = tp_shard.TPLayout(shape.num_q_heads, shape.num_kv_heads, shape.head_size, shape.intermediate, tp_size)
 
         def w(n, k):
             return (torch.randn(n, k, device=self.dev, generator=g, dtype=torch.float32) * 0.02).to(self.dtype)
 
         self.layers = []
         for _ in range(self.L):
-            lw = {
-                "qkv": self._quant_weight(w((self.Hq + 2 * self.Hkv) * self.D, H)),
-                "o": self._quant_weight(w(H, self.Hq * self.D)),
-                "gate_up": self._quant_weight(w(2 * self.inter, H)),
-                "down": self._quant_weight(w(H, self.inter)),
-                "ln1": torch.ones(H, device=self.dev, dtype=self.dtype),
-                "ln2": torch.ones(H, device=self.dev, dtype=self.dtype),
+            full = {
+                "qkv": w((shape.num_q_heads + 2 * shape.num_kv_heads) * self.D, H),
+                "o": w(H, shape.num_q_heads * self.D),
+                "gate_up": w(2 * shape.intermediate, H),
+                "down": w(H, shape.intermediate),
             }
+            shard = {
+                "qkv": lambda t: tp_shard.shard_qkv(t, lay, tp_rank),
+                "o": lambda t: tp_shard.shard_row_parallel(t, tp_size, tp_rank),
+                "gate_up": lambda t: tp_shard.shard_gate_up(t, lay, tp_rank),
+                "down": lambda t: tp_shard.shard_row_parallel(t, tp_size, tp_rank),
+            }
+            lw = {name: self._quant_weight(full[name], shard[name]) for name in full}
+            lw["ln1"] = torch.ones(H, device=self.dev, dtype=self.dtype)
+            lw["ln2"] = torch.ones(H, device=self.dev, dtype=self.dtype)
             self.layers.append(lw)
+            del full
         self.final_ln = torch.ones(H, device=self.dev, dtype=self.dtype)
-        self.embed = (torch.randn(shape.vocab, H, device=self.dev, generator=gshared, dtype=torch.float32) * 0.02).to(self.dtype)
-        self.lm_head = w(self.vocab_shard, H)
+        self.embed = w(shape.vocab, H)
+        self.lm_head = tp_shard.shard_vocab_rows(w(shape.vocab, H), tp_size, tp_rank).contiguous()
+        self.vocab_rows = self.lm_head.shape[0]  # the last vocab shard may be short
         # rotary cache [max_pos, rot_dim] = cos | sin
         inv = 1.0 / (shape.rope_theta ** (torch.arange(0, self.D, 2, device=self.dev).float() / self.D))
         fr = torch.outer(torch.arange(max_ctx + 8, device=self.dev).float(), inv)
@@ -102,12 +113,14 @@ class DecodeRunner:
         cdt = torch.uint8 if kv_cache_dtype.startswith("fp8") else self.dtype
         self.kv_caches = []
         for _ in range(self.L):
-            kv = torch.empty(2, self.num_blocks, block_size, self.Hkv, self.D, device=self.dev, dtype=cdt)
+            # the full cache (all kv heads) from the shared generator; this rank keeps its heads (tp_shard.shard_kv_cache)
+            shp = (2, self.num_blocks, block_size, shape.num_kv_heads, self.D)
             if cdt == torch.uint8:  # random finite e4m3 bytes (exponent field != 0xF)
-                kv.copy_(torch.randint(0, 256, kv.shape, device=self.dev, generator=g, dtype=torch.uint8) & 0x77)
+                kv = torch.randint(0, 256, shp, device=self.dev, generator=g, dtype=torch.uint8) & 0x77
             else:
-                kv.copy_(((torch.rand(kv.shape, device=self.dev, generator=g) * 2 - 1) * self.D ** -0.5).to(cdt))
-            self.kv_caches.append(kv)
+                kv = ((torch.rand(shp, device=self.dev, generator=g) * 2 - 1) * self.D ** -0.5).to(cdt)
+            self.kv_caches.append(tp_shard.shard_kv_cache(kv, lay, tp_rank) if tp_size > 1 else kv)
+            del kv
         self.k_scale = torch.tensor([0.05], device=self.dev)
         self.v_scale = torch.tensor([0.05], device=self.dev)
         # static step buffers (CUDA-graph inputs)
@@ -139,12 +152,14 @@ class DecodeRunner:
                 self.par = None
 
     # ----------------------------------------------------------------- weights / linears
-    def _quant_weight(self, w: torch.Tensor):
+    def _quant_weight(self, w: torch.Tensor, shard):
+        """Quantise the FULL weight (one per-tensor scale / NVFP4 global scale for the whole checkpoint tensor,
+        like a pre-quantised checkpoint) and keep this rank's shard of the quantised tensor."""
         if self.wq == "fp8":
             q, s = ops.scaled_fp8_quant(w)  # per tensor, [N,K] K-contiguous == column-major [K,N]
-            return {"w": q, "s": s}
+            return {"w": shard(q.view(torch.uint8)).contiguous().view(ops.FP8_DTYPE), "s": s}
         gs = (448.0 * 6.0 / w.abs().max().float()).reshape(1)
-        q, sf = ops.scaled_fp4_quant(w, gs)
+        q, sf = ops.scaled_fp4_quant(shard(w).contiguous(), gs)  # 16-element blocks never straddle a shard boundary
         return {"w": q, "sf": sf, "gs": gs}
 
     def _linear(self, x: torch.Tensor, lw) -> torch.Tensor:
@@ -253,6 +268,7 @@ class DecodeRunner:
         if pending:  # the last layer's down_proj: plain one-shot all-reduce, then the final norm
             hidden = self.par.all_reduce_out(1, torch.empty(B, s.hidden, device=self.dev, dtype=self.dtype))
         ops.fused_add_rms_norm(hidden, residual, self.final_ln, s.rms_eps)
+        self.last_hidden = hidden  # [B, hidden] after the final norm (TP-equivalence checks read it)
         logits = torch.matmul(hidden, self.lm_head.t())  # plain library GEMM (bf16 lm_head, as in vLLM)
         if self.tp == 1:
             self.next_tokens.copy_(logits.argmax(-1))
@@ -296,3 +312,30 @@ class DecodeRunner:
     def weight_bytes_per_layer(self) -> int:
         n = sum(lw["w"].numel() * lw["w"].element_size() for lw in self.layers[0].values() if isinstance(lw, dict))
         return n
+
+
+TP_CHECK_SHAPE = ModelShape("tp-check", 2, 1024, 16, 8, 128, 4096, 8192)
+
+
+def tp_equivalence_check(tp_size: int, tp_rank: int, group, device, *, batch: int = 16, ctx: int = 500,
+                         shape: ModelShape = TP_CHECK_SHAPE, weight_quant: str = "fp8") -> dict:
+    """Does the TP=N step compute the same function as TP=1?  Every rank builds the TP=N runner (its shard of
+    ONE seeded model) and, locally, the unsharded TP=1 runner of the same model, runs one eager step of each and
+    compares the hidden state after the final norm and the greedy tokens.  Differences come only from where the
+    dynamic per-token activation scales are taken (per shard vs whole row) and the all-reduce's summation
+    order, so the bound is a few fp8 ulps of the activations, not bit equality."""
+    one = DecodeRunner(shape, batch, ctx, tp_size=1, tp_rank=0, device=device, weight_quant=weight_quant)
+    one.set_batch(ctx)
+    t1 = one.step_eager().clone()
+    h1 = one.last_hidden.float().clone()
+    many = DecodeRunner(shape, batch, ctx, tp_size=tp_size, tp_rank=tp_rank, device=device, tp_group=group,
+                        weight_quant=weight_quant)
+    many.set_batch(ctx)
+    tn = many.step_eager().clone()
+    hn = many.last_hidden.float()
+    torch.cuda.synchronize(device)
+    rel = float((hn - h1).norm() / h1.norm())
+    # a sharded-weights mistake (wrong head / column slice) gives rel ~ 1.4 (uncorrelated vectors)
+    return {"tp": tp_size, "hidden_rel_l2": rel, "hidden_max_abs": float((hn - h1).abs().max()),
+            "tokens_equal_frac": float((tn == t1).float().mean()), "peer_allreduce": many.par is not None,
+            "weight_quant": weight_quant}

@@ -181,6 +181,12 @@ def paged_attention_decode(
         raise RuntimeError("paged_attention_decode: fp8 kv_cache_dtype needs a 1-byte cache tensor")
     if kv == KV_AUTO and key_cache.dtype != query.dtype:
         raise RuntimeError("paged_attention_decode: kv_cache_dtype='auto' needs cache dtype == query dtype")
+    for nm, sc in (("k_scale", k_scale), ("v_scale", v_scale)):
+        if sc is not None and (sc.numel() != 1 or sc.dtype != torch.float32):
+            # the decode kernel dequantises with ONE scale per tensor; a cache written with per-head scales
+            # (reshape_and_cache_flash accepts [num_heads]) would silently be read with head 0's scale
+            raise RuntimeError(f"paged_attention_decode: {nm} must be a float32 tensor with exactly one element "
+                               f"(per-head KV scales are not built), got shape {tuple(sc.shape)}")
     if num_splits <= 0:
         num_splits = paged_decode_num_splits(num_seqs, num_q_heads, num_kv_heads, max_seq_len, query.device,
                                              head_size, kv_cache_dtype)
@@ -515,6 +521,10 @@ def cutlass_scaled_fp4_mm(
 def rms_norm(out: torch.Tensor, input: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
     _require_cuda(out, input, weight)
     x = input.reshape(-1, input.shape[-1])
+    if x.stride(-1) != 1:
+        raise RuntimeError("rms_norm: input rows must be contiguous")
+    if out.dtype != input.dtype or out.numel() != input.numel() or not out.is_contiguous():
+        raise RuntimeError("rms_norm: out must be a contiguous tensor of the input's dtype and size")
     rc = _lib.load().b200_rms_norm(out.data_ptr(), x.data_ptr(), weight.data_ptr(), None, x.shape[0], x.shape[1],
                                    x.stride(0), float(epsilon), _dt(x), _stream(x))
     _lib.check(rc, "rms_norm")
@@ -523,9 +533,10 @@ def rms_norm(out: torch.Tensor, input: torch.Tensor, weight: torch.Tensor, epsil
 def fused_add_rms_norm(input: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
     """In place like the reference: residual += input (rounded), input = norm(residual) * w."""
     _require_cuda(input, residual, weight)
-    x = input.reshape(-1, input.shape[-1])
-    if not x.is_contiguous() or not residual.is_contiguous():
+    # in place: a reshape() of a non-contiguous input would silently normalise a temporary copy
+    if not input.is_contiguous() or not residual.is_contiguous():
         raise RuntimeError("fused_add_rms_norm: contiguous tensors expected")
+    x = input.view(-1, input.shape[-1])
     rc = _lib.load().b200_rms_norm(x.data_ptr(), x.data_ptr(), weight.data_ptr(), residual.data_ptr(), x.shape[0],
                                    x.shape[1], x.stride(0), float(epsilon), _dt(x), _stream(x))
     _lib.check(rc, "fused_add_rms_norm")
@@ -546,8 +557,11 @@ def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Te
     if not is_neox:
         raise RuntimeError("rotary_embedding: only the neox layout is built")
     T = positions.numel()
-    q = query.reshape(T, -1)
-    k = key.reshape(T, -1)
+    # in place: view() raises where reshape() would hand back a copy (rows may be strided slices of a fused qkv)
+    q = query.view(T, -1)
+    k = key.view(T, -1)
+    if q.stride(1) != 1 or k.stride(1) != 1:
+        raise RuntimeError("rotary_embedding: query/key rows must be contiguous")
     rc = _lib.load().b200_rotary_embedding_neox(
         q.data_ptr(), k.data_ptr(), positions.data_ptr(), cos_sin_cache.data_ptr(), T, q.shape[1] // head_size,
         k.shape[1] // head_size, head_size, cos_sin_cache.shape[1], q.stride(0), k.stride(0), _dt(q), _stream(q))
@@ -607,7 +621,7 @@ def rotary_embedding_and_cache_write(positions: torch.Tensor, query: torch.Tenso
     if not is_neox:
         raise RuntimeError("rotary_embedding_and_cache_write: only the neox layout is built")
     T = positions.numel()
-    q, k, v = query.reshape(T, -1), key.reshape(T, -1), value.reshape(T, -1)
+    q, k, v = query.view(T, -1), key.view(T, -1), value.view(T, -1)  # in place: never a reshape() copy
     if q.stride(1) != 1 or k.stride(1) != 1 or v.stride(1) != 1 or key_cache.stride(3) != 1:
         raise RuntimeError("rotary_embedding_and_cache_write: innermost dimensions must be contiguous")
     if key_cache.stride() != value_cache.stride():

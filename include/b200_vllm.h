@@ -154,6 +154,23 @@ int b200_paged_decode_pick_splits_ex(int num_seqs, int num_kv_heads, int max_seq
 int b200_paged_attention_decode(const b200_paged_decode_params* p,
                                 b200_stream_t stream);
 
+/* Allocation-free variant of b200_paged_attention_decode.  It has NO counterpart in the reference:
+ * it was added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * Same inputs, outputs and results as b200_paged_attention_decode; p->workspace / workspace_bytes are
+ * IGNORED: the split-KV partials live in a file-scope `static __device__` array of
+ * b200_paged_decode_static_scratch_bytes() = 32 MiB that every GPU which loads the library holds
+ * until the process exits.  The call allocates nothing (no cudaMalloc / cudaFree / allocator).
+ * A problem whose partials (b200_paged_decode_workspace_bytes of its split count) exceed 32 MiB is
+ * rejected with B200_ERR_WORKSPACE before any launch.
+ * Every call on a device shares the one array, which keeps the previous call's contents (nothing
+ * in it needs clearing: each slot read is written first by the same call).  Calls that OVERLAP on
+ * the GPU (two streams, or two host threads launching concurrently) race on it; serialise them on
+ * one stream or use the caller-workspace entry point. */
+size_t b200_paged_decode_static_scratch_bytes(void);
+int b200_paged_attention_decode_static_scratch(const b200_paged_decode_params* p,
+                                               b200_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * Two-way (out, lse) merge.
  * Replaces: merge_attn_states

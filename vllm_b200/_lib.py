@@ -51,6 +51,8 @@ SIGNATURES: dict[str, tuple] = {
     "b200_paged_decode_pick_splits": (i32, [i32, i32, i32, i32]),
     "b200_paged_decode_pick_splits_ex": (i32, [i32, i32, i32, i32, i32, i32]),
     "b200_paged_attention_decode": (i32, [C.POINTER(PagedDecodeParams), vp]),
+    "b200_paged_decode_static_scratch_bytes": (sz, []),
+    "b200_paged_attention_decode_static_scratch": (i32, [C.POINTER(PagedDecodeParams), vp]),
     "b200_merge_attn_states": (i32, [vp, vp, vp, vp, vp, vp, i64, i32, i32, i64, i64, i64, i64, i64, i64, i64,
                                      i32, vp]),
     "b200_static_scaled_fp8_quant": (i32, [vp, vp, vp, i64, i32, i64, i64, i32, i32, i64, i64, i32, vp]),

@@ -817,3 +817,72 @@ extern "C" int b200_paged_attention_decode(const b200_paged_decode_params* p, b2
   set_error("paged_attention_decode: no kernel for head_size %d", D);
   return B200_ERR_UNSUPPORTED;
 }
+
+// ---- allocation-free variant ---------------------------------------------------------------------
+// b200_paged_attention_decode_static_scratch: the same kernels, with the split-KV partials in a
+// file-scope device array instead of a caller workspace, for callers that cannot allocate (CUDA
+// graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The array lives in every GPU context that loads the
+// library until the process exits.
+namespace b200 {
+
+constexpr size_t kStaticScratchBytes = (size_t)32 << 20;  // 32 MiB: cfg3 TP1 needs 6.4, cfg4 5.3, cfg5 4.8
+static __device__ __align__(256) unsigned char g_decode_scratch[kStaticScratchBytes];
+
+// In host code `g_decode_scratch` is only a stand-in for the symbol, not a device address: resolve it
+// once per device, with that device current.
+static int static_scratch_ptr(void** out) {
+  static std::mutex mu;
+  static void* ptrs[64] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    set_error("paged_attention_decode_static_scratch: cudaGetDevice failed or device %d out of range: %s", dev,
+              cudaGetErrorString(e));
+    return B200_ERR_CUDA;
+  }
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_decode_scratch);
+    if (e != cudaSuccess || !p) {
+      set_error("paged_attention_decode_static_scratch: cudaGetSymbolAddress failed on device %d: %s", dev,
+                cudaGetErrorString(e));
+      return B200_ERR_CUDA;
+    }
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return 0;
+}
+
+}  // namespace b200
+
+extern "C" size_t b200_paged_decode_static_scratch_bytes(void) { return b200::kStaticScratchBytes; }
+
+extern "C" int b200_paged_attention_decode_static_scratch(const b200_paged_decode_params* p, b200_stream_t stream) {
+  using namespace b200;
+  B200_CHECK_ARG(p != nullptr, B200_ERR_INVALID_ARG, "paged_attention_decode_static_scratch: null params");
+  B200_CHECK_ARG(p->num_seqs >= 0 && p->num_q_heads > 0 && p->num_kv_heads > 0 && p->head_size > 0,
+                 B200_ERR_INVALID_ARG, "paged_attention_decode_static_scratch: bad sizes");
+  b200_paged_decode_params q = *p;
+  if (q.num_splits <= 0) {  // the split count the ordinary entry point would pick
+    const int group = q.num_q_heads / q.num_kv_heads;
+    q.num_splits = b200_paged_decode_pick_splits_ex(q.num_seqs, q.num_kv_heads * ((group + 15) / 16),
+                                                    q.max_seq_len > 0 ? q.max_seq_len : 1, sm_count(), q.head_size,
+                                                    q.kv_dtype);
+  }
+  const size_t need = b200_paged_decode_workspace_bytes(q.num_seqs, q.num_q_heads, q.head_size, q.num_splits);
+  B200_CHECK_ARG(need <= kStaticScratchBytes, B200_ERR_WORKSPACE,
+                 "paged_attention_decode_static_scratch: %d seqs x %d heads x %d splits x head_size %d needs %zu bytes "
+                 "of split-KV scratch, more than the built-in %zu; use b200_paged_attention_decode with a caller "
+                 "workspace (or fewer splits)",
+                 q.num_seqs, q.num_q_heads, q.num_splits, q.head_size, need, kStaticScratchBytes);
+  void* scratch = nullptr;
+  if (int rc = static_scratch_ptr(&scratch)) return rc;
+  // Nothing in the scratch has to start at zero: every (sequence, head, split) slot the combine kernel reads is
+  // written by this call first (an empty split writes (m, l) = (-inf, 0) and its stale accumulator is skipped).
+  q.workspace = scratch;
+  q.workspace_bytes = kStaticScratchBytes;
+  return b200_paged_attention_decode(&q, stream);
+}

@@ -19,6 +19,7 @@ import torch
 
 ROOT = Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "scripts"))
 from vllm_b200 import ops  # noqa: E402
 
 DEV = torch.device("cuda:0")
@@ -183,6 +184,26 @@ def bench_attention(ref: bool):
         rec = {"kernel": "paged_decode", "case": name, "splits": splits, "us": round(us, 2),
                "logical_gbs": round(logical / us / 1e3, 1), "frac_hbm": round(unique / us / 1e3 / HBM, 3),
                "frac_8TBps": round(unique / us / 1e3 / 8000, 3), "bytes": logical, "unique_bytes": unique}
+        if ref:
+            # the reference's own GPU kernels on the same caches / block table, same graph-replay timing
+            import ref_attention as RA
+
+            fns[0]()
+            torch.cuda.synchronize()
+            mine = out.float().clone()
+            rec["ref_us"], rec["ref_note"], rec["ref_err"], rec["ref_max_abs_diff"] = {}, {}, {}, {}
+            for rname, build in RA.BUILDERS.items():
+                try:
+                    built = [build(q, caches[i][0], caches[i][1], bt, sl, D ** -0.5, ctx, kvd, sc, sc) for i in range(ns)]
+                    rec["ref_max_abs_diff"][rname] = round(float((built[0][1].float() - mine).abs().max()), 4)
+                    rec["ref_us"][rname] = round(timeit([b[0] for b in built], reps=10), 2)
+                    rec["ref_note"][rname] = built[0][2]
+                    del built
+                except Exception as e:  # noqa: BLE001 - a reference kernel that does not run here is reported, not fatal
+                    rec["ref_err"][rname] = repr(e)[:200]
+                torch.cuda.empty_cache()
+            best = min(rec["ref_us"].values()) if rec["ref_us"] else None
+            rec["ours_over_best_ref"] = round(us / best, 3) if best else None
         emit(**rec)
         del caches
 

@@ -18,6 +18,7 @@ import argparse
 import json
 import math
 import os
+import re
 import subprocess
 import sys
 import tempfile
@@ -81,10 +82,20 @@ def worker(args) -> None:
     os.environ.setdefault("VLLM_ENABLE_V1_MULTIPROCESSING", "0")
     if not args.flat_init:
         patch_dummy_init()
-    if args.plugin:
+    # arms: stock[:BACKEND] | b200 (our attention + our linears) | b200lin:BACKEND (our linears, a stock attention
+    #       backend) | b200attn (our attention, stock linears)
+    kind = args.arm.split(":", 1)[0]
+    plugin_on = kind.startswith("b200")
+    backend = args.arm.split(":", 1)[1] if ":" in args.arm else None  # stock:TRITON_ATTN, stock:FLASHINFER, ...
+    if plugin_on:
+        if kind == "b200attn":
+            os.environ["B200_VLLM_LINEAR"] = "0"
+            os.environ["VLLM_DISABLED_KERNELS"] = "B200FP8ScaledMMLinearKernel,B200NvFp4LinearKernel"
         from vllm_b200 import plugin
 
         plugin.register()
+        if kind != "b200lin":
+            backend = "CUSTOM"
     else:
         os.environ["B200_VLLM_LINEAR"] = "0"
         os.environ["VLLM_DISABLED_KERNELS"] = "B200FP8ScaledMMLinearKernel,B200NvFp4LinearKernel"
@@ -95,23 +106,24 @@ def worker(args) -> None:
     kw = dict(model=str(d), load_format="dummy", skip_tokenizer_init=True, dtype="bfloat16", max_model_len=args.max_len,
               gpu_memory_utilization=0.3, seed=0, enforce_eager=args.eager, block_size=16,
               max_num_seqs=args.num_prompts, enable_prefix_caching=False)
-    if args.plugin:
-        kw["attention_backend"] = "CUSTOM"
-    if args.fp8:
+    if backend:
+        kw["attention_backend"] = backend
+    if args.fp8 or args.w_fp8:
         kw["quantization"] = "fp8"
+    if args.fp8 or args.kv_fp8:
         kw["kv_cache_dtype"] = "fp8"
     llm = LLM(**kw)
     g = torch.Generator().manual_seed(0)
     vocab = CONFIGS[args.model]["vocab_size"]
     prompts = [{"prompt_token_ids": torch.randint(10, vocab - 10, (args.prompt_len,), generator=g).tolist()}
                for _ in range(args.num_prompts)]
-    sp = SamplingParams(temperature=0.0, max_tokens=args.decode, logprobs=2, ignore_eos=True, detokenize=False)
+    sp = SamplingParams(temperature=0.0, max_tokens=args.decode, logprobs=5, ignore_eos=True, detokenize=False)
     outs = llm.generate(prompts, sp, use_tqdm=False)
     res = []
     for o in outs:
         c = o.outputs[0]
         toks = list(c.token_ids)
-        # per step: logprob of the sampled token, and the top-2 {token: logprob} (to judge near-ties at a divergence)
+        # per step: logprob of the sampled token, and the top-5 {token: logprob} (to judge near-ties at a divergence)
         lps = [float(lp[t].logprob) for lp, t in zip(c.logprobs, toks)]
         top = [{int(k): float(v.logprob) for k, v in lp.items()} for lp in c.logprobs]
         res.append({"tokens": toks, "logprobs": lps, "top": top})
@@ -126,50 +138,13 @@ def worker(args) -> None:
     Path(args.out).write_text(json.dumps({"results": res, "sel": sel}))
 
 
-def main() -> None:
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--model", default="opt-125m", choices=list(CONFIGS))
-    ap.add_argument("--fp8", action="store_true")
-    ap.add_argument("--eager", action="store_true")
-    ap.add_argument("--num-prompts", type=int, default=32)
-    ap.add_argument("--prompt-len", type=int, default=512)
-    ap.add_argument("--decode", type=int, default=128)
-    ap.add_argument("--max-len", type=int, default=1024)
-    ap.add_argument("--timeout", type=int, default=900)
-    ap.add_argument("--flat-init", action="store_true", help="keep vLLM's +-1e-3 dummy weights (flat logits)")
-    ap.add_argument("--worker", action="store_true")
-    ap.add_argument("--plugin", action="store_true")
-    ap.add_argument("--dir")
-    ap.add_argument("--out")
-    args = ap.parse_args()
-    if args.worker:
-        return worker(args)
-    tmp = Path(tempfile.mkdtemp(prefix="b200_e2e_"))
-    (tmp / "config.json").write_text(json.dumps(CONFIGS[args.model]))
-    (tmp / "generation_config.json").write_text(json.dumps({"_from_model_config": True}))
-    runs = {}
-    for name, plug in (("stock", False), ("b200", True)):
-        out = tmp / f"{name}.json"
-        cmd = [sys.executable, __file__, "--worker", "--model", args.model, "--dir", str(tmp), "--out", str(out),
-               "--num-prompts", str(args.num_prompts), "--prompt-len", str(args.prompt_len), "--decode", str(args.decode),
-               "--max-len", str(args.max_len)] + (["--plugin"] if plug else []) + (["--fp8"] if args.fp8 else []) + (
-                   ["--eager"] if args.eager else []) + (["--flat-init"] if args.flat_init else [])
-        env = dict(os.environ, PYTHONPATH=f"{ROOT}:{os.environ.get('PYTHONPATH', '')}")
-        r = subprocess.run(cmd, env=env, timeout=args.timeout, capture_output=True, text=True)
-        if r.returncode != 0 or not out.exists():
-            print(json.dumps({"ok": False, "stage": name, "rc": r.returncode, "tail": (r.stdout + r.stderr)[-3000:]}))
-            sys.exit(2 if name == "b200" else 3)  # 3 = the stock engine itself does not run here
-        runs[name] = json.loads(out.read_text())
-    a, b = runs["stock"]["results"], runs["b200"]["results"]
-    n_tok = sum(len(x["tokens"]) for x in a)
-    same = sum(int(t1 == t2) for x, y in zip(a, b) for t1, t2 in zip(x["tokens"], y["tokens"]))
+def compare(a, b, gap_tol: float) -> dict:
+    """Two arms' greedy streams: logprob agreement on each stream's common prefix (identical contexts) and, at the
+    first divergent step (contexts still identical), how close a call it was in EACH engine's own top-5."""
     first_div = [next((i for i, (t1, t2) in enumerate(zip(x["tokens"], y["tokens"])) if t1 != t2), len(x["tokens"]))
                  for x, y in zip(a, b)]
-    # logprob agreement on the common prefix (before any divergence the two engines saw identical contexts)
     dl = [abs(l1 - l2) for x, y, fd in zip(a, b, first_div) for l1, l2 in zip(x["logprobs"][:fd], y["logprobs"][:fd])]
-    # at a stream's first divergent step both engines still saw the same context: the step is a legitimate
-    # near-tie iff each engine ranks the other's choice second and within `gap` of its own
-    gaps, not_in_top2 = [], 0
+    gaps, missing = [], 0
     for x, y, fd in zip(a, b, first_div):
         if fd == len(x["tokens"]):
             continue
@@ -179,18 +154,77 @@ def main() -> None:
             if other in top and mine in top:
                 gaps.append(abs(top[mine] - top[other]))
             else:
-                not_in_top2 += 1
-    spread = [abs(l) for x in a for l in x["logprobs"]]
-    rep = {"ok": True, "model": args.model, "fp8": args.fp8, "eager": args.eager, "flat_init": args.flat_init,
-           "tokens": n_tok, "tokens_equal": same,
-           "streams_identical": sum(int(fd == len(x["tokens"])) for x, fd in zip(a, first_div)), "streams": len(a),
-           "common_prefix_tokens": len(dl),
-           "max_abs_logprob_diff_common_prefix": max(dl) if dl else None,
-           "mean_abs_logprob_diff_common_prefix": sum(dl) / len(dl) if dl else None,
-           "divergences": sum(int(fd < len(x["tokens"])) for x, fd in zip(a, first_div)),
-           "divergence_max_top2_gap": max(gaps) if gaps else None, "divergence_other_not_in_top2": not_in_top2,
-           "mean_abs_logprob_stock": sum(spread) / len(spread), "flat_logprob_would_be": math.log(CONFIGS[args.model]["vocab_size"]),
-           "b200": runs["b200"]["sel"], "stock": runs["stock"]["sel"]}
+                missing += 1
+    dl_sorted = sorted(dl)
+    return {"tokens": sum(len(x["tokens"]) for x in a),
+            "tokens_equal": sum(int(t1 == t2) for x, y in zip(a, b) for t1, t2 in zip(x["tokens"], y["tokens"])),
+            "streams": len(a), "streams_identical": sum(int(fd == len(x["tokens"])) for x, fd in zip(a, first_div)),
+            "common_prefix_tokens": len(dl),
+            "max_abs_logprob_diff": max(dl) if dl else None, "mean_abs_logprob_diff": sum(dl) / len(dl) if dl else None,
+            "p90_abs_logprob_diff": dl_sorted[int(0.9 * (len(dl) - 1))] if dl else None,
+            "divergences": sum(int(fd < len(x["tokens"])) for x, fd in zip(a, first_div)),
+            "divergence_max_top_gap": max(gaps) if gaps else None,
+            "divergence_mean_top_gap": sum(gaps) / len(gaps) if gaps else None,
+            "divergence_other_not_in_top5": missing,
+            "divergences_beyond_gap_tol": sum(int(g > gap_tol) for g in gaps)}
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="opt-125m", choices=list(CONFIGS))
+    ap.add_argument("--fp8", action="store_true", help="FP8 W8A8 linears AND fp8 KV cache")
+    ap.add_argument("--w-fp8", action="store_true", help="FP8 W8A8 linears only")
+    ap.add_argument("--kv-fp8", action="store_true", help="fp8 KV cache only")
+    ap.add_argument("--eager", action="store_true")
+    ap.add_argument("--num-prompts", type=int, default=32)
+    ap.add_argument("--prompt-len", type=int, default=512)
+    ap.add_argument("--decode", type=int, default=128)
+    ap.add_argument("--max-len", type=int, default=1024)
+    ap.add_argument("--timeout", type=int, default=900)
+    ap.add_argument("--flat-init", action="store_true", help="keep vLLM's +-1e-3 dummy weights (flat logits)")
+    ap.add_argument("--arms", default="stock,b200",
+                    help="comma list of engines to run: stock | stock:<ATTENTION_BACKEND> | b200; every arm is compared "
+                         "with the first one")
+    ap.add_argument("--gap-tol", type=float, default=0.5)
+    ap.add_argument("--worker", action="store_true")
+    ap.add_argument("--arm", default="stock")
+    ap.add_argument("--dir")
+    ap.add_argument("--out")
+    args = ap.parse_args()
+    if args.worker:
+        return worker(args)
+    tmp = Path(tempfile.mkdtemp(prefix="b200_e2e_"))
+    (tmp / "config.json").write_text(json.dumps(CONFIGS[args.model]))
+    (tmp / "generation_config.json").write_text(json.dumps({"_from_model_config": True}))
+    arms = args.arms.split(",")
+    runs, failed = {}, {}
+    for i, arm in enumerate(arms):
+        out = tmp / f"arm{i}.json"
+        cmd = [sys.executable, __file__, "--worker", "--arm", arm, "--model", args.model, "--dir", str(tmp), "--out", str(out),
+               "--num-prompts", str(args.num_prompts), "--prompt-len", str(args.prompt_len), "--decode", str(args.decode),
+               "--max-len", str(args.max_len)]
+        for flag in ("fp8", "w_fp8", "kv_fp8", "eager", "flat_init"):
+            if getattr(args, flag):
+                cmd.append("--" + flag.replace("_", "-"))
+        env = dict(os.environ, PYTHONPATH=f"{ROOT}:{os.environ.get('PYTHONPATH', '')}")
+        r = subprocess.run(cmd, env=env, timeout=args.timeout, capture_output=True, text=True)
+        if r.returncode != 0 or not out.exists():
+            failed[arm] = {"rc": r.returncode, "tail": (r.stdout + r.stderr)[-2500:]}
+            if i == 0 or arm.startswith("b200"):
+                print(json.dumps({"ok": False, "stage": arm, **failed[arm]}))
+                sys.exit(2 if arm.startswith("b200") else 3)  # 3 = the stock engine itself does not run here
+            continue
+        runs[arm] = json.loads(out.read_text())
+        # which kernels the engine picked, from its own log lines
+        runs[arm]["sel"]["log"] = [l.split("] ", 1)[-1][:160] for l in (r.stdout + r.stderr).splitlines()
+                                   if re.search(r"attention backend|Selected \S+ for|Using \S+ (backend|kernel)", l)][:8]
+    base = runs[arms[0]]["results"]
+    spread = [abs(l) for x in base for l in x["logprobs"]]
+    rep = {"ok": True, "model": args.model, "w_fp8": args.fp8 or args.w_fp8, "kv_fp8": args.fp8 or args.kv_fp8,
+           "eager": args.eager, "flat_init": args.flat_init, "base": arms[0],
+           "mean_abs_logprob_base": sum(spread) / len(spread), "flat_logprob_would_be": math.log(CONFIGS[args.model]["vocab_size"]),
+           "pairs": {arm: compare(base, runs[arm]["results"], args.gap_tol) for arm in arms[1:] if arm in runs},
+           "sel": {arm: runs[arm]["sel"] for arm in runs}, "arms_failed": failed}
     print(json.dumps(rep))
 
 

@@ -108,12 +108,9 @@ def _make(B, ctx, Hq, Hkv, D, bs, kv, *, seed, ragged=False, shared_prefix=False
     if kv == "auto":
         kc = ((torch.rand(nb, bs, Hkv, D, device=DEV, generator=g) * 2 - 1) * D ** -0.5).to(torch.bfloat16)
         vc = ((torch.rand(nb, bs, Hkv, D, device=DEV, generator=g) * 2 - 1) * D ** -0.5).to(torch.bfloat16)
-    else:  # random finite e4m3 bytes
-        kc = torch.randint(0, 256, (nb, bs, Hkv, D), device=DEV, generator=g, dtype=torch.uint8) & 0x77
-        vc = torch.randint(0, 256, (nb, bs, Hkv, D), device=DEV, generator=g, dtype=torch.uint8) & 0x77
-        # sign bits back (0x77 cleared bit 7 and bit 3): restore random signs
-        kc |= torch.randint(0, 2, kc.shape, device=DEV, generator=g, dtype=torch.uint8) << 7
-        vc |= torch.randint(0, 2, vc.shape, device=DEV, generator=g, dtype=torch.uint8) << 7
+    else:  # random finite e4m3 bytes of either sign, |value| <= 240 (exponent field < 0xF)
+        kc = torch.randint(0, 256, (nb, bs, Hkv, D), device=DEV, generator=g, dtype=torch.uint8) & 0xF7
+        vc = torch.randint(0, 256, (nb, bs, Hkv, D), device=DEV, generator=g, dtype=torch.uint8) & 0xF7
     q = torch.randn(B, Hq, D, device=DEV, generator=g).to(torch.bfloat16)
     if ragged:
         sl = torch.randint(ctx // 2, ctx + 1, (B,), device=DEV, generator=g, dtype=torch.int32)
@@ -143,9 +140,12 @@ def test_decode_full_size_vs_gpu_references(cuda_lib, name):
     D, bs = 128, 16
     q, kc, vc, bt, sl = _make(B, ctx, Hq, Hkv, D, bs, kv, seed=100 + list(CASES).index(name), ragged=ragged, shared_prefix=shared)
     scale = D ** -0.5
-    # power-of-two scales: the fp8 -> bf16 dequantisation some references do internally stays exact
-    ks = torch.tensor([0.0625], device=DEV) if kv != "auto" else None
-    vs = torch.tensor([0.125], device=DEV) if kv != "auto" else None
+    # power-of-two scales (the fp8 -> bf16 dequantisation some references do internally stays exact) that put
+    # K in +-3.75 and V in +-0.94: the value regime of the reference's own attention tests (uniform(+-D^-0.5)..1,
+    # torch_utils.py:621,647).  With |V| ~ 30 the legacy paged_attention_v2 kernel's bf16 probabilities alone
+    # are off by more than the 2e-2 absolute tolerance (measured: 0.25), while ours still matched the fp32 reference.
+    ks = torch.tensor([2.0 ** -6], device=DEV) if kv != "auto" else None
+    vs = torch.tensor([2.0 ** -8], device=DEV) if kv != "auto" else None
     out = torch.empty_like(q)
     splits = ops.paged_decode_num_splits(B, Hq, Hkv, ctx, torch.device(DEV), D, kv)
     ops.paged_attention_decode(out, q, kc, vc, bt, sl, scale, ctx, kv, ks, vs)  # automatic split count
@@ -155,6 +155,7 @@ def test_decode_full_size_vs_gpu_references(cuda_lib, name):
     ref = _torch_ref(q, kc, vc, bt, sl, scale, kv, float(ks) if ks is not None else 1.0,
                      float(vs) if vs is not None else 1.0)
     torch.testing.assert_close(out.float(), ref, atol=ATOL, rtol=RTOL)
+    torch.testing.assert_close(out.float(), ref, atol=4e-3, rtol=RTOL)  # vs exact fp32 math: bf16 output rounding only
     assert torch.isfinite(out.float()).all()
     # the installed reference kernels on the same tensors
     checked = []

@@ -224,3 +224,43 @@ def test_torch_ops_b200_run_on_cuda(plugin):
     torch.ops.b200.cutlass_scaled_mm(out, res, wq.t(), sc, wsc, None)
     ref = O.scaled_mm(rq, wq.cpu().t(), rs, wsc.cpu(), torch.float32)
     torch.testing.assert_close(out.cpu().float(), ref, atol=2e-2, rtol=1e-2)
+
+
+@pytest.mark.parametrize("kv_dtype", ["auto", "fp8"])
+@pytest.mark.parametrize("is_neox", [True, False])
+def test_fused_rope_kvcache_hook_matches_unfused(plugin, kv_dtype, is_neox):
+    """AttentionImpl.do_rope_and_kv_cache_update (vllm/v1/attention/backend.py:932-980) == the reference's own
+    rotary_embedding op followed by do_kv_cache_update: q, k and both cache planes bit-identical, pad slots untouched,
+    q/k/v passed as slices of the fused qkv buffer the way the model does."""
+    from vllm import _custom_ops as vops
+    from vllm_b200.attention_backend import B200AttentionBackend, B200AttentionImpl
+
+    Hq, Hkv, D, bs, nb, T = 16, 4, 128, 16, 40, 23
+    g = torch.Generator(device=DEV).manual_seed(11)
+    impl = B200AttentionImpl(Hq, D, D ** -0.5, Hkv, None, None, kv_dtype)
+    assert impl.fused_rope_kvcache_supported()
+    layer = _layer(0.05, 0.07) if kv_dtype == "fp8" else _layer()
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D, device=DEV, generator=g).to(torch.bfloat16)
+    pos = torch.randint(0, 4000, (T,), device=DEV, generator=g)
+    inv = 1.0 / (10000.0 ** (torch.arange(0, D, 2, device=DEV).float() / D))
+    fr = torch.outer(torch.arange(4096, device=DEV).float(), inv)
+    cos_sin = torch.cat([fr.cos(), fr.sin()], -1).to(torch.bfloat16)
+    slots = torch.randperm(nb * bs, device=DEV, generator=g)[:T].to(torch.int64)
+    slots[3] = -1
+    shape = B200AttentionBackend.get_kv_cache_shape(nb, bs, Hkv, D, kv_dtype)
+    cdt = torch.uint8 if kv_dtype == "fp8" else torch.bfloat16
+    kv_a = torch.zeros(shape, dtype=cdt, device=DEV)
+    kv_b = torch.zeros_like(kv_a)
+    # unfused: reference rope op, then our cache write
+    qkv_a = qkv.clone()
+    qa, ka, va = qkv_a.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+    vops.rotary_embedding(pos, qa, ka, D, cos_sin, is_neox)
+    impl.do_kv_cache_update(layer, ka.view(T, Hkv, D), va.view(T, Hkv, D), kv_a, slots)
+    # fused hook
+    qkv_b = qkv.clone()
+    qb, kb, vb = qkv_b.split([Hq * D, Hkv * D, Hkv * D], dim=-1)
+    impl.do_rope_and_kv_cache_update(layer, qb, kb, vb, pos, cos_sin, is_neox, kv_b, slots)
+    torch.cuda.synchronize()
+    assert torch.equal(qkv_a, qkv_b), "rotated q/k differ from the reference rotary_embedding op"
+    assert torch.equal(kv_a, kv_b), "cache contents differ from the unfused write"
+    assert kv_b.any()

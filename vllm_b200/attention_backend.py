@@ -223,7 +223,12 @@ class B200AttentionBackend(AttentionBackend):
 
 
 class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
-    can_return_lse_for_decode: bool = True
+    # The C ABI returns the softmax LSE (natural log, b200_paged_decode_params.out_lse; tested), but `forward` does not
+    # run the decode-context-parallel flow (all-gather q -> local context attention -> cp_lse_ag_out_rs -> merge,
+    # flash_attn.py:1178-1330), so the capability is NOT advertised: with DCP > 1 vLLM refuses this backend at
+    # start-up (vllm/v1/attention/backend.py:791-816,861) instead of silently computing shard-local attention.
+    can_return_lse_for_decode: bool = False
+    supports_dcp: bool = False
 
     def __init__(self, num_heads: int, head_size: int, scale: float, num_kv_heads: int | None = None,
                  alibi_slopes: list[float] | None = None, sliding_window: int | None = None,
@@ -270,6 +275,34 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
         # num_tokens = slot_mapping.size(0), key/value may be longer (CUDA-graph padding)
         ops.reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping, self.kv_cache_dtype,
                                     layer._k_scale, layer._v_scale)
+
+    # ---- RoPE + KV-cache write in one launch (vllm/v1/attention/backend.py:932-980).  Called by
+    # torch.ops.vllm.fused_rope_and_unified_kv_cache_update (compilation/passes/fusion/rope_kvcache_fusion.py:39-70)
+    # when RopeKVCacheFusionPass has replaced rotary_embedding + unified_kv_cache_update.  NOTE: the reference's own
+    # config gate keeps that pass off outside ROCm (vllm/config/compilation.py:293-298), so on CUDA the hook is
+    # reachable through the op / a direct call until that gate opens.
+    def fused_rope_kvcache_supported(self) -> bool:
+        return True
+
+    def do_rope_and_kv_cache_update(self, layer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                                    positions: torch.Tensor, cos_sin_cache: torch.Tensor, is_neox: bool,
+                                    kv_cache: torch.Tensor, layer_slot_mapping: torch.Tensor) -> None:
+        """In place: query/key rotated, (rotated key, value) written to the paged cache at layer_slot_mapping.
+        Bit-identical to rotary_embedding followed by do_kv_cache_update (tests/test_gpu_vllm_plugin.py)."""
+        if not is_neox or kv_cache.numel() == 0:
+            # GPT-J style rotation is not built into the fused kernel: rotate with the reference's own op, then
+            # our cache write (still one launch fewer than nothing, and always correct)
+            from vllm import _custom_ops as vops
+
+            vops.rotary_embedding(positions, query, key, self.head_size, cos_sin_cache, is_neox)
+            if kv_cache.numel():
+                self.do_kv_cache_update(layer, key.view(-1, self.num_kv_heads, self.head_size),
+                                        value.view(-1, self.num_kv_heads, self.head_size), kv_cache, layer_slot_mapping)
+            return
+        key_cache, value_cache = self._split_cache(kv_cache)
+        ops.rotary_embedding_and_cache_write(positions, query, key, value, self.head_size, cos_sin_cache, key_cache,
+                                             value_cache, layer_slot_mapping, self.kv_cache_dtype, layer._k_scale,
+                                             layer._v_scale)
 
     def forward(self, layer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, kv_cache: torch.Tensor,
                 attn_metadata: B200AttentionMetadata, output: torch.Tensor | None = None,

@@ -10,7 +10,17 @@
 // ([rowTile][kTile][32][4][4] = 512 B per atom), so a stage's 4 atoms are one
 // contiguous 2 KB cp.async.bulk; tcgen05.cp.32x128b.warpx4 moves each atom into 4 TMEM
 // columns (double-buffered by stage parity) right before the MMA that reads it.
+//
+// Decode regime (M <= 256, weight-bandwidth bound; the reference's small-M configs are
+// nvfp4_scaled_mm_kernels.cu:46-74,214-248): swap-AB - 128 weight rows on UMMA-M, the (padded) tokens on
+// UMMA-N = 16..256 - and, because N/128 tiles alone leave most SMs idle (70B TP8 qkv: 10 tiles), CLUSTER SPLIT-K:
+// the S <= 8 CTAs of a cluster take consecutive K ranges of one tile; every CTA parks its fp32 partial in its own
+// (now idle) pipeline ring, the cluster synchronises, and CTA s finishes the s-th share of the token chunks by
+// pulling the S partials over distributed shared memory and adding them in split order (deterministic, no
+// workspace, no atomics).
 #include <cuda.h>
+
+#include <cstdlib>
 
 #include "umma.cuh"
 
@@ -45,7 +55,27 @@ struct F4Args {
   int64_t ldc;
   int M, N, K;
   int num_k_atoms;  // ceil(K / 64)
+  int splits;       // cluster split-K factor (swap-AB decode regime), 1 otherwise
 };
+
+__device__ __forceinline__ uint32_t f4_cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void f4_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float4 f4_ld_dsmem(uint32_t local_addr, uint32_t cta) {
+  uint32_t ra;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(local_addr), "r"(cta));
+  float4 v;
+  asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(ra)
+               : "memory");
+  return v;
+}
 
 __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
@@ -63,6 +93,30 @@ __device__ __forceinline__ uint64_t make_sf_desc(uint32_t smem_addr) {
   return d;
 }
 
+// 16 consecutive outputs of one row: two 16-byte stores when the chunk is whole and aligned
+template <typename OutT>
+__device__ __forceinline__ void f4_store_row16(OutT* dst, const float (&v)[16], float alpha, int valid) {
+  if (valid >= 16 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if constexpr (std::is_same<OutT, __nv_bfloat16>::value) {
+        __nv_bfloat162 p = __floats2bfloat162_rn(v[2 * i] * alpha, v[2 * i + 1] * alpha);
+        w[i] = *reinterpret_cast<uint32_t*>(&p);
+      } else {
+        __half2 p = __floats2half2_rn(v[2 * i] * alpha, v[2 * i + 1] * alpha);
+        w[i] = *reinterpret_cast<uint32_t*>(&p);
+      }
+    }
+    reinterpret_cast<uint4*>(dst)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    reinterpret_cast<uint4*>(dst)[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      if (j < valid) dst[j] = from_float<OutT>(v[j] * alpha);
+  }
+}
+
 template <int BN, bool kSwap, typename OutT>
 __global__ void __launch_bounds__(kF4Threads, 1)
     nvfp4_gemm_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_y,
@@ -77,9 +131,13 @@ __global__ void __launch_bounds__(kF4Threads, 1)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int x0 = blockIdx.x * 128, y0 = blockIdx.y * BN;
+  const int S = g.splits;
+  const int split = S > 1 ? (int)f4_cluster_ctarank() : 0;
+  const int xt = S > 1 ? (int)blockIdx.x / S : (int)blockIdx.x;  // X tile index
+  const int x0 = xt * 128, y0 = blockIdx.y * BN;
   const int k_bytes = g.K / 2;
-  const int nkb = (k_bytes + kF4BK - 1) / kF4BK;
+  const int nkb_total = (k_bytes + kF4BK - 1) / kF4BK;
+  const int kb_begin = nkb_total * split / S, kb_end = nkb_total * (split + 1) / S;
   const int y_rows = kSwap ? g.M : g.N;
   const int y_tiles_total = (y_rows + 127) / 128;
 
@@ -107,7 +165,7 @@ __global__ void __launch_bounds__(kF4Threads, 1)
       uint32_t phase = 0;
       const uint64_t hint_x = kSwap ? kEvictFirst : kEvictLast;
       const uint64_t hint_y = kSwap ? kEvictLast : kEvictFirst;
-      for (int kb = 0; kb < nkb; ++kb) {
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sx = smem + stage * Cfg::STAGE_BYTES;
         uint8_t* sy = sx + Cfg::X_BYTES;
@@ -121,7 +179,7 @@ __global__ void __launch_bounds__(kF4Threads, 1)
         mbar_arrive_expect_tx(&full_bar[stage], bytes);
         tma_load_2d(sx, &tmap_x, &full_bar[stage], kb * kF4BK, x0, hint_x);
         tma_load_2d(sy, &tmap_y, &full_bar[stage], kb * kF4BK, y0, hint_y);
-        bulk_load_1d(ssfx, g.sfx + ((int64_t)blockIdx.x * g.num_k_atoms + 4 * kb) * kAtomBytes, atoms * kAtomBytes,
+        bulk_load_1d(ssfx, g.sfx + ((int64_t)xt * g.num_k_atoms + 4 * kb) * kAtomBytes, atoms * kAtomBytes,
                      &full_bar[stage]);
 #pragma unroll
         for (int t = 0; t < Cfg::YT; ++t) {
@@ -141,7 +199,7 @@ __global__ void __launch_bounds__(kF4Threads, 1)
       constexpr uint32_t idesc = umma::make_idesc_nvf4(128, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
-      for (int kb = 0; kb < nkb; ++kb) {
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
         mbar_wait(&full_bar[stage], phase);
         umma::fence_after_sync();
         const uint32_t sx = smem_u32(smem + stage * Cfg::STAGE_BYTES);
@@ -160,7 +218,7 @@ __global__ void __launch_bounds__(kF4Threads, 1)
             umma::cp_32x128b_warpx4(t_sfy + 4 * Cfg::YT * kk + 4 * t,
                                     make_sf_desc(ssfy + t * 4 * kAtomBytes + kk * kAtomBytes));
           umma::mma_nvf4_block16(tmem_base, umma::desc_advance(dx, kk * 32), umma::desc_advance(dy, kk * 32), idesc,
-                                 (kb | kk) != 0, t_sfx + 4 * kk, t_sfy + 4 * Cfg::YT * kk);
+                                 (kb != kb_begin) || (kk != 0), t_sfx + 4 * kk, t_sfy + 4 * Cfg::YT * kk);
         }
         umma::commit(&empty_bar[stage]);
         if (++stage == STAGES) {
@@ -179,6 +237,23 @@ __global__ void __launch_bounds__(kF4Threads, 1)
     const int y_lim = kSwap ? g.M : g.N;
     OutT* outp = reinterpret_cast<OutT*>(g.out);
     const float alpha = *g.alpha;
+    if (S > 1) {
+      // cluster split-K: park this CTA's fp32 partial in the idle ring, [chunk][j/4][128 rows] float4 so that a
+      // warp's stores (and the peers' remote loads) are 512 contiguous bytes
+      float4* park = reinterpret_cast<float4*>(smem);
+      const int et = q * 32 + lane;
+      const int nch = (min(BN, y_lim - y0) + 15) >> 4;
+#pragma unroll 1
+      for (int ch = 0; ch < nch; ++ch) {
+        uint32_t r[16];
+        umma::ld_32x32b_x16(tmem_base + ((uint32_t)(q * 32) << 16) + ch * 16, r);
+        umma::ld_wait();
+#pragma unroll
+        for (int j4 = 0; j4 < 4; ++j4)
+          park[(ch * 4 + j4) * 128 + et] = make_float4(__uint_as_float(r[j4 * 4]), __uint_as_float(r[j4 * 4 + 1]),
+                                                       __uint_as_float(r[j4 * 4 + 2]), __uint_as_float(r[j4 * 4 + 3]));
+      }
+    } else
 #pragma unroll 1
     for (int c = 0; c < BN; c += 16) {
       uint32_t r[16];
@@ -216,17 +291,75 @@ __global__ void __launch_bounds__(kF4Threads, 1)
       }
     }
   }
+  if (S > 1) {
+    f4_cluster_sync();  // every partial of the cluster is parked and visible cluster-wide
+    if (warp >= 2) {
+      const int q = warp & 3, et = q * 32 + lane, xi = x0 + et;
+      const int x_lim = kSwap ? g.N : g.M, y_lim = kSwap ? g.M : g.N;
+      const int nch = (min(BN, y_lim - y0) + 15) >> 4;
+      const int own_lo = nch * split / S, own_hi = nch * (split + 1) / S;
+      OutT* outp = reinterpret_cast<OutT*>(g.out);
+      const float alpha = *g.alpha;
+      const uint32_t park0 = smem_u32(smem);
+#pragma unroll 1
+      for (int ch = own_lo; ch < own_hi; ++ch) {
+        float v[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = 0.f;
+#pragma unroll 1
+        for (int sp = 0; sp < S; ++sp) {  // split order: the sum does not depend on which CTA finishes the chunk
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4) {
+            const float4 t = f4_ld_dsmem(park0 + (uint32_t)(((ch * 4 + j4) * 128 + et) * 16), (uint32_t)sp);
+            v[j4 * 4 + 0] += t.x, v[j4 * 4 + 1] += t.y, v[j4 * 4 + 2] += t.z, v[j4 * 4 + 3] += t.w;
+          }
+        }
+        if (xi >= x_lim) continue;
+        if constexpr (kSwap) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int m = y0 + ch * 16 + j;
+            if (m < g.M) outp[(int64_t)m * g.ldc + xi] = from_float<OutT>(v[j] * alpha);
+          }
+        } else {
+          f4_store_row16<OutT>(outp + (int64_t)xi * g.ldc + y0 + ch * 16, v, alpha, y_lim - (y0 + ch * 16));
+        }
+      }
+    }
+    f4_cluster_sync();  // peers may still be reading this CTA's ring
+  }
   umma::fence_before_sync();
   __syncthreads();
   if (warp == 1) umma::tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
 template <int BN, bool kSwap, typename OutT>
-static int launch_f4(const CUtensorMap& tx, const CUtensorMap& ty, const F4Args& g, dim3 grid, cudaStream_t stream) {
+static int launch_f4(const CUtensorMap& tx, const CUtensorMap& ty, const F4Args& g, dim3 grid, cudaStream_t stream,
+                     int* max_clusters_query = nullptr) {
   using Cfg = F4Cfg<BN>;
   auto kern = nvfp4_gemm_kernel<BN, kSwap, OutT>;
   if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES)) return rc_attr;
-  launch_kernel(kern, dim3(grid), dim3(kF4Threads), Cfg::SMEM_BYTES, stream, 1, tx, ty, g);
+  if (max_clusters_query) {  // how many clusters of g.splits CTAs are co-resident on this device
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(g.splits, 1, 1);
+    cfg.blockDim = dim3(kF4Threads, 1, 1);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = g.splits;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) {
+      cudaGetLastError();
+      n = 0;
+    }
+    *max_clusters_query = n;
+    return 0;
+  }
+  launch_kernel(kern, dim3(grid), dim3(kF4Threads), Cfg::SMEM_BYTES, stream, g.splits, tx, ty, g);
   B200_CHECK_LAUNCH();
   count_launch();
   return 0;
@@ -246,19 +379,50 @@ static int run_f4(void* out, const void* a, const void* b, const void* sfa, cons
   CUtensorMap tx, ty;
   int rc;
   const int kb = K / 2;
+  g.splits = 1;
+  const int nkb = (kb + kF4BK - 1) / kF4BK;
+  static const int s_cap = [] {
+    const char* e = getenv("B200_F4_SMAX");  // tuning aid: largest cluster split-K factor (1 = off)
+    return (e && *e) ? atoi(e) : 8;
+  }();
+  // cluster split-K factor: the largest S <= 8 that keeps base x S CTAs co-resident in ONE wave with >= 4 k-blocks
+  // per split (measured: with fewer the two cluster barriers + the DSMEM reduce cost more than the shorter K loop
+  // saves - o_proj K = 1024 went 5.3 -> 6.3 us with S = 2)
+  auto pick_splits = [&](long base_ctas, auto&& query_max_clusters) -> int {
+    for (int s = s_cap < 8 ? s_cap : 8; s >= 2; --s) {
+      if (nkb / s < 4 || base_ctas * s > sm_count()) continue;
+      if (query_max_clusters(s) >= base_ctas) return s;
+    }
+    return 1;
+  };
   if (M <= 128) {
     const int bn = M <= 16 ? 16 : (M <= 32 ? 32 : (M <= 64 ? 64 : 128));
     g.sfx = reinterpret_cast<const uint8_t*>(sfb);
     g.sfy = reinterpret_cast<const uint8_t*>(sfa);
     if ((rc = get_kmajor_tmap(&tx, b, N, kb, kb, 128))) return rc;
     if ((rc = get_kmajor_tmap(&ty, a, M, kb, kb, bn))) return rc;
-    dim3 grid((N + 127) / 128, 1, 1);
-    switch (bn) {
-      case 16: return launch_f4<16, true, OutT>(tx, ty, g, grid, stream);
-      case 32: return launch_f4<32, true, OutT>(tx, ty, g, grid, stream);
-      case 64: return launch_f4<64, true, OutT>(tx, ty, g, grid, stream);
-      default: return launch_f4<128, true, OutT>(tx, ty, g, grid, stream);
-    }
+    const int tiles = (N + 127) / 128;
+    auto dispatch = [&](dim3 grid, int* query) -> int {
+      switch (bn) {
+        case 16: return launch_f4<16, true, OutT>(tx, ty, g, grid, stream, query);
+        case 32: return launch_f4<32, true, OutT>(tx, ty, g, grid, stream, query);
+        case 64: return launch_f4<64, true, OutT>(tx, ty, g, grid, stream, query);
+        default: return launch_f4<128, true, OutT>(tx, ty, g, grid, stream, query);
+      }
+    };
+    static int max_active[4][9] = {};  // [bn index][S]: 0 not queried, -1 unsupported
+    const int bi = bn == 16 ? 0 : bn == 32 ? 1 : bn == 64 ? 2 : 3;
+    const int S = pick_splits(tiles, [&](int s) {
+      if (max_active[bi][s] == 0) {
+        int n = 0;
+        g.splits = s;
+        if (dispatch(dim3(1, 1, 1), &n)) n = 0;
+        max_active[bi][s] = n > 0 ? n : -1;
+      }
+      return max_active[bi][s];
+    });
+    g.splits = S;
+    return dispatch(dim3(tiles * S, 1, 1), nullptr);
   }
   g.sfx = reinterpret_cast<const uint8_t*>(sfa);
   g.sfy = reinterpret_cast<const uint8_t*>(sfb);
@@ -267,7 +431,20 @@ static int run_f4(void* out, const void* a, const void* b, const void* sfa, cons
   if (bn == 256 && (long)((M + 127) / 128) * ((N + 255) / 256) < sm_count()) bn = 128;
   if ((rc = get_kmajor_tmap(&tx, a, M, kb, kb, 128))) return rc;
   if ((rc = get_kmajor_tmap(&ty, b, N, kb, kb, bn))) return rc;
-  dim3 grid((M + 127) / 128, (N + bn - 1) / bn, 1);
+  const int mt = (M + 127) / 128, nt = (N + bn - 1) / bn;
+  if (bn == 128) {  // few tiles (e.g. 70B TP8 qkv at M = 256: 20): cluster split-K along K, clusters laid along x
+    static int max_active128[9] = {};
+    g.splits = pick_splits((long)mt * nt, [&](int s) {
+      if (max_active128[s] == 0) {
+        int n = 0;
+        g.splits = s;
+        if (launch_f4<128, false, OutT>(tx, ty, g, dim3(1, 1, 1), stream, &n)) n = 0;
+        max_active128[s] = n > 0 ? n : -1;
+      }
+      return max_active128[s];
+    });
+  }
+  dim3 grid(mt * g.splits, nt, 1);
   if (bn == 256) return launch_f4<256, false, OutT>(tx, ty, g, grid, stream);
   return launch_f4<128, false, OutT>(tx, ty, g, grid, stream);
 }

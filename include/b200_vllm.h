@@ -141,6 +141,11 @@ typedef struct b200_paged_decode_params {
   float scale;                /* softmax scale                               */
   float logits_soft_cap;      /* 0 = off                                     */
   int sliding_window;         /* 0 = off; else attend to last W tokens       */
+  /* Fused static FP8 output quant (AttentionImpl.forward(output_scale=...), vllm/v1/attention/backend.py:910-922,
+   * quant key kFp8StaticTensorSym): when non-NULL, `out` is e4m3 BYTES (strides in bytes) and every output element
+   * is stored as e4m3_rn_sat(o * (1 / *output_scale)) straight from the fp32 accumulator - no bf16 round trip and no
+   * separate quant launch in front of o_proj.  NULL = out in the query dtype. */
+  const float* output_scale;
 } b200_paged_decode_params;
 
 size_t b200_paged_decode_workspace_bytes(int num_seqs, int num_q_heads,
@@ -257,12 +262,10 @@ int b200_scaled_mm_fp8(void* out, const void* a, const void* b,
                        int64_t ldb, int64_t ldc, int a_scales_numel,
                        int b_scales_numel, int out_dtype, void* workspace,
                        size_t workspace_bytes, b200_stream_t stream);
-/* Split-K / stream-K fix-up scratch for the decode regime (M <= 256): 2 KB of
- * per-CTA flags followed by one fp32 [BN][128] partial tile per CTA.  Zero the
- * first 2 KB ONCE after allocation; the kernels leave the flags zeroed.  Must be
- * 16-byte aligned and must not be shared by GEMMs running concurrently on
- * different streams.  workspace == NULL: every CTA takes whole 128-row weight
- * tiles (no K split), which leaves SMs idle when N/128 < #SMs. */
+/* Scratch size for b200_scaled_mm_fp8: always 0 since round 2 - the decode regime's split-K fix-up is a
+ * reduce-scatter over distributed shared memory inside one thread-block cluster, and the large-M kernels need
+ * none.  `workspace` / `workspace_bytes` of b200_scaled_mm_fp8 are accepted and ignored (kept so that callers
+ * written against the round-1 ABI keep working). */
 size_t b200_scaled_mm_workspace_bytes(int M, int N);
 
 /* ------------------------------------------------------------------------
@@ -377,6 +380,22 @@ int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, const uint6
                                         void* residual, float epsilon, int64_t num_tokens, int hidden, int dtype,
                                         b200_stream_t stream);
 
+/* NVLS variants (in-switch reduction): the same two operations with ONE `multimem.ld_reduce` per 16 bytes instead
+ * of world_size peer loads - the NVSwitch adds the ranks' copies with fp32 accumulation and returns the sum rounded
+ * once to the element type.  multicast_ptr = the multicast mapping of the same symmetric allocation
+ * (torch.distributed._symmetric_memory handle.multicast_ptr; 0 when the fabric has no multicast support -> error).
+ * Reference analogue: vllm/distributed/device_communicators/symm_mem.py:137-150 (torch.ops.symm_mem.
+ * multimem_all_reduce_) and the fused AR+RMSNorm of flashinfer_all_reduce.py.  Same call-order and
+ * buffer-alternation rules as the peer-load entries; world sizes 2..8, incl. the fused form at 8 ranks. */
+int b200_nvls_all_reduce_out(void* out, uint64_t multicast_ptr, const uint64_t* peer_buffers,
+                             const uint64_t* peer_signal_pads, int rank, int world_size, int64_t numel,
+                             int dtype, int64_t byte_offset, int64_t signal_pad_bytes, b200_stream_t stream);
+int b200_nvls_all_reduce_rms_norm_quant(void* result, float* scales, uint64_t multicast_ptr,
+                                        const uint64_t* peer_buffers, const uint64_t* peer_signal_pads,
+                                        int rank, int world_size, int64_t byte_offset, int64_t signal_pad_bytes,
+                                        const void* weight, void* residual, float epsilon, int64_t num_tokens,
+                                        int hidden, int dtype, b200_stream_t stream);
+
 /* Spin budget of one cross-rank barrier wait, in polls (default 2^28, minutes); 0 = wait for ever.  A rank
  * that exceeds it prints a message and traps instead of hanging the GPU. */
 void b200_peer_set_barrier_timeout(unsigned long long max_polls);
@@ -402,8 +421,8 @@ void b200_debug_attn_trace(unsigned long long* device_buffer);
 /* fp8-cache decode kernel selection (tests / tuning): 1 = tcgen05 kernel, 0 = register-level kernel,
  * -1 = default (register-level unless B200_ATTN_FP8_TCGEN05=1). */
 void b200_debug_attn_fp8_tcgen05(int mode);
-/* Force the decode-regime work partition (tests / tuning): 0 whole tiles, 1 stream-K and 2 split-K
- * through the workspace, 3 cluster split-K over distributed shared memory, -1 automatic. */
+/* Force the decode-regime work partition (tests / tuning): 0 whole tiles per CTA pair, 3 cluster split-K over
+ * distributed shared memory, -1 automatic. */
 void b200_debug_gemm_mode(int mode);
 
 #ifdef __cplusplus

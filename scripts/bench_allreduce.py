@@ -55,9 +55,17 @@ def one():
     par.all_reduce_out(flip[0], o1); flip[0] ^= 1
 one(); torch.cuda.synchronize()
 err1 = (o1.float() - ref.float()).abs().max().item()
-one_us, g3 = timed(one)
+one_us, g3 = timed(one)   # NVLS (multimem.ld_reduce) when the fabric has multicast, else peer loads
+nvls = bool(par.multicast_ptr)
+peer_one_us = None
+if nvls:
+    mc, par.multicast_ptr = par.multicast_ptr, 0
+    peer_one_us, g4 = timed(one)
+    par.multicast_ptr = mc
 if rank == 0:
-    print(f"world {world}: 1 MB bf16 all-reduce  NCCL {nccl_us:.1f} us  peer two-shot {peer_us:.1f} us  one-shot {one_us:.1f} us (err {err1:.4f})  "
+    extra = f"one-shot peer loads {peer_one_us:.1f} us  " if peer_one_us is not None else ""
+    print(f"world {world}: 1 MB bf16 all-reduce  NCCL {nccl_us:.1f} us  peer two-shot {peer_us:.1f} us  "
+          f"one-shot{' NVLS' if nvls else ''} {one_us:.1f} us (err {err1:.4f})  {extra}"
           f"max|peer - nccl| {err:.4f}  run-to-run identical {same}  (signal pad {par._pad_bytes} B)", flush=True)
 del g1, g2, g3
 torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()

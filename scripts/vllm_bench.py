@@ -70,6 +70,20 @@ def worker(a) -> None:
         return time.perf_counter() - t0, sum(len(o.outputs[0].token_ids) for o in outs)
 
     run(8)  # warm-up: graphs captured, lazy modules loaded
+    if a.profile:
+        # per-kernel device time of ~48 decode steps (CUPTI sees the kernels inside replayed CUDA graphs)
+        from torch.profiler import ProfilerActivity, profile
+
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            run(48)
+        rows = sorted(((e.key, e.count, e.device_time_total) for e in prof.key_averages() if e.device_time_total > 0),
+                      key=lambda r: -r[2])
+        tot = sum(r[2] for r in rows)
+        lines = [f"# arm {a.arm}: {tot / 1e3:.1f} ms of kernels over prefill + 48 decode steps of batch {a.batch}",
+                 f"{'total_ms':>9} {'n':>6} {'avg_us':>8} {'share':>6}  kernel"]
+        for k, n, t in rows[:40]:
+            lines.append(f"{t / 1e3:9.2f} {n:6d} {t / n:8.2f} {100 * t / tot:5.1f}%  {k[:150]}")
+        Path(a.profile).write_text("\n".join(lines) + "\n")
     t_short, n_short = run(16)          # prefill + 16 decode steps
     t_long, n_long = run(a.decode)      # prefill + `decode` steps
     # decode-only rate: the two runs share the same prefill, the difference is (decode - 16) steps of all requests
@@ -92,6 +106,8 @@ def main() -> None:
     ap.add_argument("--decode", type=int, default=4032)
     ap.add_argument("--arms", default="stock,b200")
     ap.add_argument("--timeout", type=int, default=1500)
+    ap.add_argument("--profile", default="", help="directory: also write a per-kernel device-time table per arm")
+    ap.add_argument("--log-dir", default="", help="directory: keep every arm's full engine log")
     ap.add_argument("--worker", action="store_true")
     ap.add_argument("--arm", default="stock")
     ap.add_argument("--dir")
@@ -107,12 +123,18 @@ def main() -> None:
         out = tmp / f"arm{i}.json"
         cmd = [sys.executable, __file__, "--worker", "--arm", arm, "--dir", str(tmp), "--out", str(out), "--batch", str(a.batch),
                "--prompt-len", str(a.prompt_len), "--decode", str(a.decode)]
+        if a.profile:
+            Path(a.profile).mkdir(parents=True, exist_ok=True)
+            cmd += ["--profile", str(Path(a.profile) / f"vllm_kernels_{arm.replace(':', '_')}.txt")]
         env = dict(os.environ, PYTHONPATH=f"{ROOT}:{os.environ.get('PYTHONPATH', '')}")
         try:
             r = subprocess.run(cmd, env=env, timeout=a.timeout, capture_output=True, text=True)
         except subprocess.TimeoutExpired:
             res[arm] = {"error": f"timed out after {a.timeout} s"}
             continue
+        if a.log_dir:
+            Path(a.log_dir).mkdir(parents=True, exist_ok=True)
+            (Path(a.log_dir) / f"vllm_log_{arm.replace(':', '_')}.txt").write_text(r.stdout + r.stderr)
         if r.returncode != 0 or not out.exists():
             res[arm] = {"error": f"rc={r.returncode}", "tail": (r.stdout + r.stderr)[-1500:]}
             continue

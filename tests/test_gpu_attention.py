@@ -348,3 +348,45 @@ def test_decode_vs_installed_vllm_kernels(ops):
     torch.ops._C.paged_attention_v1(out, q.to(DEV), k_leg, v_leg, Hkv, scale, bt.to(DEV), sl.to(DEV), bs,
                                     int(sl.max()), None, "auto", one, one, 0, 0, 0, 64, 0)
     torch.testing.assert_close(mine, out.cpu().float(), atol=ATOL, rtol=RTOL)
+
+
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+@pytest.mark.parametrize("splits", [1, 3])
+def test_decode_fused_static_fp8_output_quant(ops, kv, splits):
+    """forward(output_scale=...) semantics (vllm/v1/attention/backend.py:910-922, kFp8StaticTensorSym): the output is
+    e4m3(o * (1 / output_scale)) taken from the fp32 result.  Against the oracle's attention followed by the oracle's
+    static quant: identical bytes except where the two fp32 results straddle a rounding boundary (then one e4m3 step
+    apart); against our own unfused path the same.  Empty sequences give zero bytes."""
+    S, Hq, Hkv, D, bs = 7, 32, 8, 128, 16
+    lens = [333, 1, 0, 1000, 64, 17, 512]
+    q, kc, vc, bt, sl, scale = _rand_case(31, S, Hq, Hkv, D, bs, lens, torch.bfloat16)
+    ks = vs = None
+    if kv == "fp8":
+        ks, vs = torch.tensor([0.02]), torch.tensor([0.03])
+        kc = O.to_fp8(kc.float() / ks).view(torch.uint8)
+        vc = O.to_fp8(vc.float() / vs).view(torch.uint8)
+    ref = O.paged_attention_decode(q, kc, vc, bt, sl, scale, kv, 1.0 if ks is None else float(ks),
+                                   1.0 if vs is None else float(vs))
+    out_scale = torch.tensor([ref.abs().max().item() / 300.0])
+    expect = O.to_fp8(ref * (1.0 / out_scale))
+    out = torch.full((S, Hq, D), 0x7F, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn)
+    ops.paged_attention_decode(out, q.to(DEV), kc.to(DEV), vc.to(DEV), bt.to(DEV), sl.to(DEV), scale, max(lens), kv,
+                               None if ks is None else ks.to(DEV), None if vs is None else vs.to(DEV),
+                               num_splits=splits, output_scale=out_scale.to(DEV))
+    torch.cuda.synchronize()
+    got = out.cpu()
+    # 1. what matters: the dequantised output is the attention result within the attention tolerance plus half an
+    #    e4m3 step (2^-4 relative) of quantisation error
+    torch.testing.assert_close(got.float() * out_scale, ref, atol=3e-3, rtol=0.07)
+    # 2. and it is the SAME quantiser as the oracle's static quant of its own fp32 result: most bytes identical, the
+    #    rest one or two steps apart (the two fp32 attention results differ by ~1e-3, several steps near zero)
+    same = (got.view(torch.uint8) == expect.view(torch.uint8)).float().mean().item()
+    assert same > 0.93, f"only {same:.4f} of the fp8 bytes match the oracle"
+    assert not torch.any(got.view(torch.uint8) == 0x7F)  # every element written, none NaN
+    assert torch.all(got.view(torch.uint8)[2] == 0)  # the empty sequence
+    # a bf16 `out` together with output_scale is refused
+    with pytest.raises(RuntimeError, match="output_scale"):
+        ops.paged_attention_decode(torch.empty(S, Hq, D, dtype=torch.bfloat16, device=DEV), q.to(DEV), kc.to(DEV),
+                                   vc.to(DEV), bt.to(DEV), sl.to(DEV), scale, max(lens), kv,
+                                   None if ks is None else ks.to(DEV), None if vs is None else vs.to(DEV),
+                                   output_scale=out_scale.to(DEV))

@@ -105,8 +105,8 @@ def test_emulated_all_reduce_rms_norm_quant(cuda_lib, world):
 
 
 # ------------------------------------------------------------------------------- real ranks
-def _worker(rank, world, port, q):
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+def _worker(rank, world, port, q, nvls):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), B200_NVLS="1" if nvls else "0")
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
@@ -115,6 +115,9 @@ def _worker(rank, world, port, q):
 
     B, H = 48, 1024
     par = PeerAllReduce(dist.group.WORLD, dev, 2, B * H)
+    used_nvls = bool(par.multicast_ptr)
+    if nvls and not used_nvls and rank == 0:
+        print("NVLS requested but the fabric exposes no multicast mapping: peer-load path tested instead", flush=True)
     g = torch.Generator(device=dev).manual_seed(7 + rank)
     ok = True
     for it in range(6):
@@ -152,14 +155,17 @@ def _worker(rank, world, port, q):
         ok = ok and torch.equal(xq.view(torch.uint8), xq_ref.view(torch.uint8)) and torch.equal(xs, xs_ref)
         ok = ok and torch.equal(res_f, res_ref)
     if rank == 0:
-        q.put(ok)
+        q.put((ok, used_nvls))
     torch.cuda.synchronize()
     dist.barrier()
     os._exit(0)
 
 
+@pytest.mark.parametrize("nvls", [True, False])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_peer_all_reduce_real_ranks(world):
+def test_peer_all_reduce_real_ranks(world, nvls):
+    """nvls=True: multimem.ld_reduce (in-switch sum) when torch's symmetric memory exposes a multicast mapping;
+    nvls=False: the peer-load kernels (B200_NVLS=0)."""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     with socket.socket() as s:
@@ -167,9 +173,11 @@ def test_peer_all_reduce_real_ranks(world):
         port = s.getsockname()[1]
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q, nvls)) for r in range(world)]
     for p in procs:
         p.start()
-    assert q.get(timeout=300)
+    ok, used_nvls = q.get(timeout=300)
     for p in procs:
         p.join(timeout=60)
+    print(f"world {world}: nvls requested {nvls}, used {used_nvls}")
+    assert ok

@@ -138,9 +138,10 @@ def _fp8_kernel(act_key, w_key, n, k):
         return B200FP8ScaledMMLinearKernel(c, ["weight", "weight_scale", "input_scale", "input_scale_ub"])
 
 
+@pytest.mark.parametrize("own_quant", [False, True])
 @pytest.mark.parametrize("static_act", [False, True])
 @pytest.mark.parametrize("m", [1, 128, 300])
-def test_fp8_linear_kernel_against_installed_cutlass(plugin, static_act, m):
+def test_fp8_linear_kernel_against_installed_cutlass(plugin, static_act, m, own_quant, monkeypatch):
     """B200FP8ScaledMMLinearKernel.apply_weights == vLLM's quant + cutlass_scaled_mm on the same layer."""
     from vllm import _custom_ops as vops
     from vllm.model_executor.layers.quantization.utils import quant_utils as Q
@@ -155,8 +156,16 @@ def test_fp8_linear_kernel_against_installed_cutlass(plugin, static_act, m):
                                   input_scale=torch.tensor([0.02], device=DEV) if static_act else None, input_scale_ub=None)
     kern = _fp8_kernel(Q.kFp8StaticTensorSym if static_act else Q.kFp8DynamicTokenSym, Q.kFp8StaticTensorSym, n, k)
     kern.process_weights_after_loading(layer)
+    # own_quant False: activation quant by vLLM's QuantFP8 (the default, fusible by Inductor); True: our quant ops
+    from vllm_b200 import linear_kernels
+
+    monkeypatch.setattr(linear_kernels, "_OWN_QUANT", own_quant)
     y = kern.apply_weights(layer, x, bias)
-    if static_act:
+    if not own_quant:
+        # the reference quantises with the SAME QuantFP8 object the kernel class inherited (in eager mode its native
+        # torch formula, which rounds a few elements differently from the _C kernel): only the GEMM differs
+        xq, xs = kern.quant_fp8(x, layer.input_scale, None)
+    elif static_act:
         xq, xs = vops.scaled_fp8_quant(x, layer.input_scale)
     else:
         xq, xs = vops.scaled_fp8_quant(x, use_per_token_if_dynamic=True)

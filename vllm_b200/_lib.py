@@ -36,6 +36,7 @@ class PagedDecodeParams(C.Structure):
         ("head_size", i32), ("block_size", i32), ("max_seq_len", i32),
         ("q_dtype", i32), ("kv_dtype", i32), ("num_splits", i32),
         ("scale", f32), ("logits_soft_cap", f32), ("sliding_window", i32),
+        ("output_scale", vp),
     ]
 
 
@@ -72,6 +73,9 @@ SIGNATURES: dict[str, tuple] = {
     "b200_peer_all_reduce": (i32, [vp, vp, i32, i32, i64, i32, i64, i64, vp]),
     "b200_peer_all_reduce_out": (i32, [vp, vp, vp, i32, i32, i64, i32, i64, i64, vp]),
     "b200_peer_all_reduce_rms_norm_quant": (i32, [vp, vp, vp, vp, i32, i32, i64, i64, vp, vp, f32, i64, i32, i32, vp]),
+    "b200_nvls_all_reduce_out": (i32, [vp, C.c_uint64, vp, vp, i32, i32, i64, i32, i64, i64, vp]),
+    "b200_nvls_all_reduce_rms_norm_quant": (i32, [vp, vp, C.c_uint64, vp, vp, i32, i32, i64, i64, vp, vp, f32, i64, i32,
+                                                  i32, vp]),
     "b200_peer_set_barrier_timeout": (None, [C.c_ulonglong]),
     "b200_set_pdl": (None, [i32]),
     "b200_get_pdl": (i32, []),

@@ -310,8 +310,8 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
                 ) -> torch.Tensor:
         """query [T, Hq, D] (or [T, Hq*D]); writes output[:num_actual_tokens] in place and returns it."""
         assert output is not None, "Output tensor must be provided."
-        if output_scale is not None or output_block_scale is not None:
-            raise NotImplementedError("B200 attention backend: fused output quantisation is not built")
+        if output_block_scale is not None:
+            raise NotImplementedError("B200 attention backend: fused NVFP4 (block-scaled) output quantisation is not built")
         if attn_metadata is None:  # profiling run (flash_attn.py:915-917)
             return output.fill_(0)
         md = attn_metadata
@@ -333,5 +333,15 @@ class B200AttentionImpl(AttentionImpl[B200AttentionMetadata]):
             o, q, key_cache, value_cache, md.block_table, seq_lens, self.scale, md.max_seq_len, self.kv_cache_dtype,
             layer._k_scale if fp8 else None, layer._v_scale if fp8 else None, num_splits=md.num_splits,
             workspace=md.workspace, logits_soft_cap=self.logits_soft_cap, sliding_window=self.sliding_window,
-            token_to_seq=token_to_seq)
+            token_to_seq=token_to_seq, output_scale=output_scale)
         return output
+
+    def fused_output_quant_supported(self, quant_key) -> bool:
+        """AttnFusionPass asks before folding the static FP8 quant in front of o_proj into attention
+        (vllm/v1/attention/backend.py:910-922; reference impls triton_attn.py:453, flashinfer.py:1349).  Static
+        per-tensor symmetric FP8 is written straight from the split-combine / epilogue; NVFP4 output is not built."""
+        try:
+            from vllm.model_executor.layers.quantization.utils.quant_utils import kFp8StaticTensorSym
+        except Exception:
+            return False
+        return quant_key == kFp8StaticTensorSym

@@ -31,6 +31,7 @@ SOURCES = [
     "fused_quant.cu",
     "fp8_gemm.cu",
     "fp8_gemm_decode.cu",
+    "gemm_persist.cu",
     "nvfp4_gemm.cu",
     "peer_allreduce.cu",
 ]

@@ -13,6 +13,7 @@
 // persistent 2-CTA kernel in gemm_persist.cu when the shape allows, else to the kernel below.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -271,6 +272,12 @@ int run_fp8_decode(void* out, const void* a, const void* b, const float* a_scale
                    const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc, int a_scales_numel,
                    int b_scales_numel, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 
+// large M: persistent 2-CTA kernel (gemm_persist.cu); returns 1 when it does not take the shape
+template <typename OutT>
+int run_fp8_gemm_2sm(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
+                     const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc, int a_scales_numel,
+                     int b_scales_numel, cudaStream_t stream);
+
 template <typename OutT>
 static int run_fp8_gemm(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
                         const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
@@ -290,6 +297,15 @@ static int run_fp8_gemm(void* out, const void* a, const void* b, const float* a_
   if (M <= 256)
     return run_fp8_decode<OutT>(out, a, b, a_scales, b_scales, bias, M, N, K, lda, ldb, ldc, a_scales_numel,
                                 b_scales_numel, workspace, workspace_bytes, stream);
+  static const bool use_2sm = [] {
+    const char* e = getenv("B200_GEMM_2SM");  // tuning aid: 0 = one-tile-per-CTA kernel below
+    return !(e && *e && atoi(e) == 0);
+  }();
+  if (use_2sm) {
+    const int r2 = run_fp8_gemm_2sm<OutT>(out, a, b, a_scales, b_scales, bias, M, N, K, lda, ldb, ldc, a_scales_numel,
+                                          b_scales_numel, stream);
+    if (r2 <= 0) return r2;
+  }
   CUtensorMap tx, ty;
   int rc;
   int bn = (N % 256 == 0 || N > 2048) ? 256 : 128;

@@ -170,22 +170,29 @@ __global__ void __launch_bounds__(1024) peer_allreduce_rms_norm_quant_kernel(
     uint8_t* dst = out + (int64_t)row * hidden;
     float ss = 0.f;
     for (int v = threadIdx.x; v < nv; v += blockDim.x) {
-      uint4 in[kArMaxWorld];
+      float acc[N];
+      if (a.mc) {  // NVLS: in-switch sum over the ranks (fp32 accumulation, rounded to T once)
+        const uint4 sm = multimem_ld_reduce_add<T>(reinterpret_cast<const uint4*>(a.mc) + (int64_t)row * nv + v);
+        const T* e = reinterpret_cast<const T*>(&sm);
 #pragma unroll
-      for (int q = 0; q < kArMaxWorld; ++q)
-        if (q < a.world) in[q] = reinterpret_cast<const uint4*>(a.bufs[q])[(int64_t)row * nv + v];
+        for (int i = 0; i < N; ++i) acc[i] = to_float(e[i]);
+      } else {
+        uint4 in[kArMaxWorld];
+#pragma unroll
+        for (int q = 0; q < kArMaxWorld; ++q)
+          if (q < a.world) in[q] = reinterpret_cast<const uint4*>(a.bufs[q])[(int64_t)row * nv + v];
+#pragma unroll
+        for (int i = 0; i < N; ++i) acc[i] = 0.f;
+#pragma unroll
+        for (int q = 0; q < kArMaxWorld; ++q)
+          if (q < a.world) {
+            const T* e = reinterpret_cast<const T*>(&in[q]);
+#pragma unroll
+            for (int i = 0; i < N; ++i) acc[i] += to_float(e[i]);
+          }
+      }
       const uint4 rr = *reinterpret_cast<const uint4*>(res + v * N);
       const T* rv = reinterpret_cast<const T*>(&rr);
-      float acc[N];
-#pragma unroll
-      for (int i = 0; i < N; ++i) acc[i] = 0.f;
-#pragma unroll
-      for (int q = 0; q < kArMaxWorld; ++q)
-        if (q < a.world) {
-          const T* e = reinterpret_cast<const T*>(&in[q]);
-#pragma unroll
-          for (int i = 0; i < N; ++i) acc[i] += to_float(e[i]);
-        }
       uint4 o;
       T* ov = reinterpret_cast<T*>(&o);
 #pragma unroll
@@ -497,11 +504,10 @@ extern "C" int b200_rotary_embedding_and_cache_write(
   });
 }
 
-extern "C" int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, const uint64_t* peer_buffers,
-                                                   const uint64_t* peer_signal_pads, int rank, int world_size,
-                                                   int64_t byte_offset, int64_t signal_pad_bytes, const void* weight,
-                                                   void* residual, float epsilon, int64_t num_tokens, int hidden,
-                                                   int dtype, b200_stream_t stream) {
+static int ar_rms_norm_quant_impl(void* result, float* scales, const uint64_t* peer_buffers,
+                                  const uint64_t* peer_signal_pads, int rank, int world_size, int64_t byte_offset,
+                                  int64_t signal_pad_bytes, const void* weight, void* residual, float epsilon,
+                                  int64_t num_tokens, int hidden, int dtype, b200_stream_t stream, uint64_t multicast_ptr) {
   using namespace b200;
   B200_CHECK_ARG(result && scales && peer_buffers && peer_signal_pads && weight && residual, B200_ERR_INVALID_ARG,
                  "peer_all_reduce_rms_norm_quant: null pointer");
@@ -530,6 +536,7 @@ extern "C" int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, 
   a.spin_limit = ar_spin_limit();
   a.emu = emu ? 1 : 0;
   a.emu_stride = num_tokens * hidden;
+  a.mc = (multicast_ptr && !emu) ? reinterpret_cast<const void*>(multicast_ptr + byte_offset) : nullptr;
   return dispatch16f(dtype, "peer_all_reduce_rms_norm_quant", [&](auto tag) {
     using T = decltype(tag);
     if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(peer_allreduce_rms_norm_quant_kernel<T>), 49152 * 4)) return rc_attr;
@@ -541,4 +548,26 @@ extern "C" int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, 
     count_launch();
     return 0;
   });
+}
+
+extern "C" int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, const uint64_t* peer_buffers,
+                                                   const uint64_t* peer_signal_pads, int rank, int world_size,
+                                                   int64_t byte_offset, int64_t signal_pad_bytes, const void* weight,
+                                                   void* residual, float epsilon, int64_t num_tokens, int hidden,
+                                                   int dtype, b200_stream_t stream) {
+  return ar_rms_norm_quant_impl(result, scales, peer_buffers, peer_signal_pads, rank, world_size, byte_offset,
+                                signal_pad_bytes, weight, residual, epsilon, num_tokens, hidden, dtype, stream, 0);
+}
+
+extern "C" int b200_nvls_all_reduce_rms_norm_quant(void* result, float* scales, uint64_t multicast_ptr,
+                                                   const uint64_t* peer_buffers, const uint64_t* peer_signal_pads,
+                                                   int rank, int world_size, int64_t byte_offset,
+                                                   int64_t signal_pad_bytes, const void* weight, void* residual,
+                                                   float epsilon, int64_t num_tokens, int hidden, int dtype,
+                                                   b200_stream_t stream) {
+  B200_CHECK_ARG(multicast_ptr != 0 && (multicast_ptr + byte_offset) % 16 == 0, B200_ERR_INVALID_ARG,
+                 "nvls_all_reduce_rms_norm_quant: no (aligned) multicast mapping - NVLS unavailable");
+  return ar_rms_norm_quant_impl(result, scales, peer_buffers, peer_signal_pads, rank, world_size, byte_offset,
+                                signal_pad_bytes, weight, residual, epsilon, num_tokens, hidden, dtype, stream,
+                                multicast_ptr);
 }

@@ -1,0 +1,314 @@
+// Persistent 2-CTA (cta_group::2) FP8 GEMM for the compute-bound regime (M > 256):
+//   out[M,N] = a_s[M|1] * b_s[N|1] * (A[M,K] @ B[N,K]^T) (+ bias[N]),  fp8 e4m3 operands, fp32 accumulate in TMEM.
+// Reference semantics: cutlass_scaled_mm (scaled_mm_entry.cu:197-270); the reference's sm100 large-M config is
+// c3x/scaled_mm_sm100_fp8_dispatch.cuh:100-116 (256x128x128 tile, 2x2 cluster, 2-SM MMA).
+//
+// B200 design
+//  * a CLUSTER OF TWO CTAs (one TPC) computes a 256 x BN output tile with ONE tcgen05.mma.cta_group::2 stream issued
+//    by the leader CTA: UMMA M = 256 (CTA r owns token rows 128r..128r+127 in its TMEM lanes), UMMA N = BN = 256;
+//    each CTA TMA-loads only ITS 128 rows of A and ITS BN/2 rows of B per k-block (32 KB) - the tensor core reads
+//    the other half of B out of the peer's shared memory, so per-SM shared-memory fill is half of what two
+//    independent 128 x BN tiles would need (the measured per-SM ingest cap is ~125 GB/s, profiles/r02_*).
+//  * PERSISTENT: one cluster per TPC, static round-robin over the output tiles (M fastest, so clusters running at
+//    the same time share the weight tile in L2); the smem ring keeps streaming across tile boundaries.
+//  * two TMEM accumulators (2 x 256 columns = all of TMEM): the epilogue of tile i (tcgen05.ld -> scales -> bf16 ->
+//    global) runs while the MMAs of tile i+1 fill the other accumulator.
+//  * warp roles per CTA: warp 0 TMA producer, warp 1 TMEM allocator + (leader only) MMA issuer, warps 2-5 epilogue
+//    (one per TMEM lane quarter).  Barriers: full[] lives in the leader (both CTAs' TMA bytes land on it),
+//    empty[] / tmem_full[] are per CTA and signalled by multicast tcgen05.commit, tmem_empty[] lives in the leader
+//    and counts the epilogue warps of BOTH CTAs.
+#include <cuda.h>
+
+#include "umma.cuh"
+
+namespace b200 {
+
+int get_kmajor_tmap(CUtensorMap* out, const void* base, int rows, int k_bytes, int64_t ld_bytes, int box_rows);
+
+constexpr int kP2Threads = 192;
+constexpr int kP2BK = 128;  // bytes of K per stage (one 128-byte swizzle span = 128 fp8)
+
+template <int BN> struct P2Cfg {
+  static constexpr int A_BYTES = 128 * kP2BK;         // this CTA's 128 token rows
+  static constexpr int B_BYTES = (BN / 2) * kP2BK;    // this CTA's half of the weight tile
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
+  static constexpr int TMEM_COLS = 2 * BN <= 32 ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/;
+  static_assert(2 * BN <= 512, "two accumulators must fit the 512 TMEM columns");
+};
+
+struct P2Args {
+  void* out;
+  const float* a_scales;  // per token (M) or [1]
+  const float* b_scales;  // per channel (N) or [1]
+  const void* bias;       // [N] out dtype or null
+  int64_t ldc;
+  int M, N, K;
+  int a_scales_numel, b_scales_numel;
+  int tiles_m, tiles_n, num_kb;
+};
+
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // shared::cluster address of the same offset in CTA rank 0 of the pair
+
+__device__ __forceinline__ uint32_t p2_cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void p2_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA load whose completion bytes are counted on the LEADER CTA's mbarrier (executed by both CTAs of the pair)
+__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const void* tmap, uint64_t* bar, int c0, int c1,
+                                                uint64_t hint) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar) & kPeerBitMask), "r"(c0), "r"(c1), "l"(hint)
+      : "memory");
+}
+__device__ __forceinline__ void mma_f8f6f4_2sm(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                               uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive (once all MMAs issued so far have completed) on the barrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void commit_2sm(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                   smem_u32(bar)),
+               "h"((uint16_t)3)
+               : "memory");
+}
+// arrive on the barrier at this offset in the LEADER CTA (local arrive when executed by the leader)
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerBitMask)
+               : "memory");
+}
+template <int kCols> __device__ __forceinline__ void tmem_alloc_2sm(uint32_t* smem_result) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_result)),
+               "n"(kCols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+template <int kCols> __device__ __forceinline__ void tmem_dealloc_2sm(uint32_t taddr) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "n"(kCols) : "memory");
+}
+
+template <typename OutT> __device__ __forceinline__ uint32_t p2_pack2(float a, float b);
+template <> __device__ __forceinline__ uint32_t p2_pack2<__nv_bfloat16>(float a, float b) {
+  const __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&t);
+}
+template <> __device__ __forceinline__ uint32_t p2_pack2<__half>(float a, float b) {
+  const __half2 t = __floats2half2_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&t);
+}
+
+template <int BN, typename OutT>
+__global__ void __launch_bounds__(kP2Threads, 1)
+    fp8_gemm_2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                        const P2Args g) {
+  using Cfg = P2Cfg<BN>;
+  constexpr int STAGES = Cfg::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem_1024(smem_raw);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;  // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = (int)p2_cluster_ctarank();  // 0 = leader (issues the MMAs)
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int num_tiles = g.tiles_m * g.tiles_n;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);   // the leader's arrive.expect_tx covers BOTH CTAs' bytes (see the producer)
+      mbar_init(&empty_bar[s], 1);  // multicast tcgen05.commit
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full_bar[b], 1);   // multicast tcgen05.commit
+      mbar_init(&tmem_empty_bar[b], 8);  // 4 epilogue warps x 2 CTAs (used in the leader only)
+    }
+    fence_barrier_init();
+    prefetch_tensormap(&tmap_a);
+    prefetch_tensormap(&tmap_b);
+  }
+  if (warp == 1) tmem_alloc_2sm<Cfg::TMEM_COLS>(tmem_slot);
+  umma::fence_before_sync();
+  p2_cluster_sync();  // both CTAs' barriers are initialised before any remote arrive / multicast commit
+  umma::fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();
+  pdl_wait();
+
+  if (warp == 0) {
+    // ===== TMA producer (both CTAs): my 128 rows of A, my BN/2 rows of B =====
+    if (umma::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = pair; t < num_tiles; t += num_pairs) {
+        const int tm = t % g.tiles_m, tn = t / g.tiles_m;
+        const int a_row = tm * 256 + rank * 128, b_row = tn * BN + rank * (BN / 2);
+        for (int kb = 0; kb < g.num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+          // Byte counting alone synchronises the pair: the leader expects both CTAs' bytes; the peer only issues
+          // its loads (complete_tx on the leader's barrier).  The peer cannot run ahead into the next phase of
+          // this slot because its own empty[] barrier is signalled by the MMAs that consumed the current one.
+          // (A remote mbarrier.arrive.release.cluster here compiled to MEMBAR.ALL.CTA + ERRBAR per k-block in the
+          // one thread that issues the peer's loads: 0.8 us per k-block, 35 % tensor-pipe utilisation -
+          // profiles/r02_gemm2sm_ncu.md.)
+          if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
+          tma_load_2d_2sm(sa, &tmap_a, &full_bar[stage], kb * kP2BK, a_row, kEvictNormal);
+          tma_load_2d_2sm(sa + Cfg::A_BYTES, &tmap_b, &full_bar[stage], kb * kP2BK, b_row, kEvictNormal);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (leader CTA only) =====
+    if (rank == 0 && umma::elect_one()) {
+      constexpr uint32_t idesc = umma::make_idesc_f8(256, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+        const int acc = it & 1;
+        mbar_wait(&tmem_empty_bar[acc], (((uint32_t)it >> 1) & 1) ^ 1);  // both CTAs' epilogues drained this buffer
+        umma::fence_after_sync();
+        const uint32_t tacc = tmem_base + acc * BN;
+        for (int kb = 0; kb < g.num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          umma::fence_after_sync();
+          const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+          const uint64_t da = umma::make_desc_k_sw128(sa);
+          const uint64_t db = umma::make_desc_k_sw128(sa + Cfg::A_BYTES);
+#pragma unroll
+          for (int kk = 0; kk < kP2BK / 32; ++kk)
+            mma_f8f6f4_2sm(tacc, umma::desc_advance(da, kk * 32), umma::desc_advance(db, kk * 32), idesc,
+                           (kb | kk) != 0);
+          commit_2sm(&empty_bar[stage]);  // frees the slot in both CTAs
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        commit_2sm(&tmem_full_bar[acc]);  // accumulator complete: both CTAs' epilogues may drain their halves
+      }
+    }
+  } else {
+    // ===== epilogue (both CTAs): warp w owns TMEM lanes 32*(w%4).. = token rows of this CTA's half =====
+    const int q = warp & 3;
+    OutT* outp = reinterpret_cast<OutT*>(g.out);
+    const OutT* bias = reinterpret_cast<const OutT*>(g.bias);
+    const bool vec_ok = ((g.ldc * (int64_t)sizeof(OutT)) % 16 == 0) && (reinterpret_cast<uintptr_t>(g.out) % 16 == 0);
+    const float bs0 = g.b_scales[0];
+    int it = 0;
+    for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+      const int tm = t % g.tiles_m, tn = t / g.tiles_m;
+      const int acc = it & 1;
+      const int m = tm * 256 + rank * 128 + q * 32 + lane;
+      const int n0 = tn * BN;
+      const float as = m < g.M ? g.a_scales[g.a_scales_numel > 1 ? m : 0] : 0.f;
+      mbar_wait(&tmem_full_bar[acc], ((uint32_t)it >> 1) & 1);
+      umma::fence_after_sync();
+      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+      uint32_t rn[16];
+      umma::ld_32x32b_x16(tacc, rn);
+#pragma unroll 1
+      for (int c = 0; c < BN; c += 16) {
+        umma::ld_wait_dep(rn);
+        float v[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(rn[j]);
+        if (c + 16 < BN) umma::ld_32x32b_x16(tacc + c + 16, rn);  // next chunk in flight while this one is stored
+        const int n = n0 + c;
+        if (m < g.M && n < g.N) {  // N % 16 == 0: a chunk is entirely inside or outside
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float bs = g.b_scales_numel > 1 ? g.b_scales[n + j] : bs0;
+            v[j] = v[j] * as * bs + (bias ? to_float(bias[n + j]) : 0.f);
+          }
+          OutT* dst = outp + (int64_t)m * g.ldc + n;
+          if (vec_ok) {
+            uint32_t w[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) w[i] = p2_pack2<OutT>(v[2 * i], v[2 * i + 1]);
+            reinterpret_cast<uint4*>(dst)[0] = make_uint4(w[0], w[1], w[2], w[3]);
+            reinterpret_cast<uint4*>(dst)[1] = make_uint4(w[4], w[5], w[6], w[7]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) dst[j] = from_float<OutT>(v[j]);
+          }
+        }
+      }
+      umma::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_leader(&tmem_empty_bar[acc]);
+    }
+  }
+  umma::fence_before_sync();
+  p2_cluster_sync();  // the leader's MMAs read the peer's shared memory; multicast arrives target both CTAs
+  if (warp == 1) tmem_dealloc_2sm<Cfg::TMEM_COLS>(tmem_base);
+}
+
+template <int BN, typename OutT>
+static int launch_p2(const CUtensorMap& ta, const CUtensorMap& tb, const P2Args& g, int num_pairs, cudaStream_t stream) {
+  using Cfg = P2Cfg<BN>;
+  auto kern = fp8_gemm_2sm_kernel<BN, OutT>;
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES)) return rc;
+  launch_kernel(kern, dim3(2 * num_pairs), dim3(kP2Threads), Cfg::SMEM_BYTES, stream, 2, ta, tb, g);
+  B200_CHECK_LAUNCH();
+  count_launch();
+  return 0;
+}
+
+// Returns 1 when the shape is not handled here (the caller falls back to the one-tile-per-CTA kernel), 0 on
+// success, a negative B200_ERR_* otherwise.
+template <typename OutT>
+int run_fp8_gemm_2sm(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
+                     const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc, int a_scales_numel,
+                     int b_scales_numel, cudaStream_t stream) {
+  constexpr int BN = 256;
+  if (M <= 256 || N < BN / 2) return 1;
+  P2Args g;
+  g.out = out;
+  g.a_scales = a_scales;
+  g.b_scales = b_scales;
+  g.bias = bias;
+  g.ldc = ldc;
+  g.M = M;
+  g.N = N;
+  g.K = K;
+  g.a_scales_numel = a_scales_numel;
+  g.b_scales_numel = b_scales_numel;
+  g.tiles_m = (M + 255) / 256;
+  g.tiles_n = (N + BN - 1) / BN;
+  g.num_kb = (K + kP2BK - 1) / kP2BK;
+  CUtensorMap ta, tb;
+  int rc;
+  if ((rc = get_kmajor_tmap(&ta, a, M, K, lda, 128))) return rc;
+  if ((rc = get_kmajor_tmap(&tb, b, N, K, ldb, BN / 2))) return rc;
+  const int tiles = g.tiles_m * g.tiles_n;
+  int pairs = sm_count() / 2;
+  if (pairs > tiles) pairs = tiles;
+  return launch_p2<BN, OutT>(ta, tb, g, pairs, stream);
+}
+
+template int run_fp8_gemm_2sm<__nv_bfloat16>(void*, const void*, const void*, const float*, const float*, const void*,
+                                             int, int, int, int64_t, int64_t, int64_t, int, int, cudaStream_t);
+template int run_fp8_gemm_2sm<__half>(void*, const void*, const void*, const float*, const float*, const void*, int, int,
+                                      int, int64_t, int64_t, int64_t, int, int, cudaStream_t);
+
+}  // namespace b200

@@ -148,9 +148,14 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
         a.part_ml[((int64_t)seq * a.num_q_heads + qh0 + threadIdx.x) * a.num_splits + split] =
             make_float2(-INFINITY, 0.f);
     } else {
-      QT* o = reinterpret_cast<QT*>(a.out) + (int64_t)seq * a.out_stride_seq + (int64_t)qh0 * a.out_stride_head;
-      for (int i = threadIdx.x; i < rows * D; i += blockDim.x)
-        o[(int64_t)(i / D) * a.out_stride_head + (i % D)] = from_float<QT>(0.f);
+      if (a.out_scale) {  // e4m3 zero is the zero byte
+        uint8_t* o = reinterpret_cast<uint8_t*>(a.out) + (int64_t)seq * a.out_stride_seq + (int64_t)qh0 * a.out_stride_head;
+        for (int i = threadIdx.x; i < rows * D; i += blockDim.x) o[(int64_t)(i / D) * a.out_stride_head + (i % D)] = 0;
+      } else {
+        QT* o = reinterpret_cast<QT*>(a.out) + (int64_t)seq * a.out_stride_seq + (int64_t)qh0 * a.out_stride_head;
+        for (int i = threadIdx.x; i < rows * D; i += blockDim.x)
+          o[(int64_t)(i / D) * a.out_stride_head + (i % D)] = from_float<QT>(0.f);
+      }
       if (a.out_lse && (int)threadIdx.x < rows)
         a.out_lse[(int64_t)seq * a.num_q_heads + qh0 + threadIdx.x] = -INFINITY;
     }
@@ -504,8 +509,14 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
       a.part_o[pi * D + d] = acc;
       if (d == 0) a.part_ml[pi] = make_float2(mt, lt);
     } else {
-      QT* op = reinterpret_cast<QT*>(a.out) + (int64_t)seq * a.out_stride_seq + (int64_t)qh * a.out_stride_head;
-      op[d] = from_float<QT>(lt > 0.f ? acc / lt * vscale : 0.f);
+      const float ov = lt > 0.f ? acc / lt * vscale : 0.f;
+      if (a.out_scale) {
+        reinterpret_cast<uint8_t*>(a.out)[(int64_t)seq * a.out_stride_seq + (int64_t)qh * a.out_stride_head + d] =
+            to_e4m3_sat(ov * (1.0f / *a.out_scale));
+      } else {
+        QT* op = reinterpret_cast<QT*>(a.out) + (int64_t)seq * a.out_stride_seq + (int64_t)qh * a.out_stride_head;
+        op[d] = from_float<QT>(ov);
+      }
       if (d == 0 && a.out_lse)
         a.out_lse[(int64_t)seq * a.num_q_heads + qh] = lt > 0.f ? (mt + log2f(lt)) * kLn2 : -INFINITY;
     }
@@ -518,8 +529,8 @@ __global__ void __launch_bounds__(kWarps * 32, OccFor<DecodeCfg<D, KV>::SMEM_BYT
 template <typename QT>
 __global__ void __launch_bounds__(128) paged_decode_combine_kernel(
     QT* __restrict__ out, float* __restrict__ out_lse, const float* __restrict__ part_o,
-    const float2* __restrict__ part_ml, const float* __restrict__ v_scale, int num_q_heads, int num_splits, int D,
-    int64_t out_stride_seq, int64_t out_stride_head) {
+    const float2* __restrict__ part_ml, const float* __restrict__ v_scale, const float* __restrict__ out_scale,
+    int num_q_heads, int num_splits, int D, int64_t out_stride_seq, int64_t out_stride_head) {
   pdl_trigger();
   pdl_wait();
   // one warp per (sequence, head), four heads per CTA; a lane owns 4 consecutive d (16-byte partial loads,
@@ -538,6 +549,23 @@ __global__ void __launch_bounds__(128) paged_decode_combine_kernel(
   lt = warp_sum(lt);
   const float vs = v_scale ? *v_scale : 1.f;
   const float inv = lt > 0.f ? vs / lt : 0.f;
+  if (out_scale) {
+    // fused static FP8 output quant: e4m3(o * (1 / output_scale)) from the fp32 accumulator, 4 bytes per lane
+    uint8_t* ob = reinterpret_cast<uint8_t*>(out) + (int64_t)seq * out_stride_seq + (int64_t)h * out_stride_head;
+    const float qs = inv * (1.0f / *out_scale);
+    for (int d = lane * 4; d < D; d += 128) {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      for (int i = 0; i < num_splits; ++i) {
+        const float mi = part_ml[base + i].x;
+        if (mi == -INFINITY) continue;
+        const float wgt = fast_exp2(mi - mt);
+        for (int e = 0; e < 4 && d + e < D; ++e) acc[e] += part_o[(base + i) * D + d + e] * wgt;
+      }
+      for (int e = 0; e < 4 && d + e < D; ++e) ob[d + e] = to_e4m3_sat(acc[e] * qs);
+    }
+    if (lane == 0 && out_lse) out_lse[(int64_t)seq * num_q_heads + h] = lt > 0.f ? (mt + log2f(lt)) * kLn2 : -INFINITY;
+    return;
+  }
   QT* op = out + (int64_t)seq * out_stride_seq + (int64_t)h * out_stride_head;
   const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(op) & 7) == 0);
   if (vec) {
@@ -628,7 +656,7 @@ static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const Dec
     const char* e = getenv("B200_ATTN_FP8_TCGEN05");
     return !(e && *e && atoi(e) != 0);
   }();
-  const bool legacy_fp8 = g_fp8_tcgen05 >= 0 ? (g_fp8_tcgen05 == 0) : env_legacy;
+  const bool legacy_fp8 = a.out_scale ? true : (g_fp8_tcgen05 >= 0 ? (g_fp8_tcgen05 == 0) : env_legacy);
   if (KV != B200_KV_AUTO && !legacy_fp8) {
     // fp8 caches run on tcgen05 (paged_decode_fp8.cu)
     if constexpr (KV != B200_KV_AUTO && D != 64) {
@@ -645,7 +673,7 @@ static int launch_decode(const CUtensorMap& tk, const CUtensorMap& tv, const Dec
     dim3 g2((a.num_q_heads + 3) / 4, num_seqs);
     launch_kernel(paged_decode_combine_kernel<QT>, dim3(g2), dim3(128), 0, stream, 1, 
         reinterpret_cast<QT*>(a.out), a.out_lse, a.part_o, a.part_ml, KV == B200_KV_AUTO ? nullptr : a.v_scale,
-        a.num_q_heads, a.num_splits, D, a.out_stride_seq, a.out_stride_head);
+        a.out_scale, a.num_q_heads, a.num_splits, D, a.out_stride_seq, a.out_stride_head);
     B200_CHECK_LAUNCH();
     count_launch();
   }
@@ -744,6 +772,7 @@ extern "C" int b200_paged_attention_decode(const b200_paged_decode_params* p, b2
   a.k_scale = p->k_scale;
   a.v_scale = p->v_scale;
   a.out_lse = p->out_lse;
+  a.out_scale = p->output_scale;
   a.token_to_seq = p->token_to_seq;
   a.q_stride_seq = p->q_stride_seq;
   a.q_stride_head = p->q_stride_head;

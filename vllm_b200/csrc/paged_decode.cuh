@@ -20,6 +20,7 @@ struct DecodeArgs {
   const float* k_scale;
   const float* v_scale;
   float* out_lse;
+  const float* out_scale;  // non-null: `out` is e4m3 bytes, o * (1 / *out_scale) (fused static output quant)
   const int32_t* token_to_seq;  // optional: block_table row per query token
   float* part_o;   // [seq][hq][split][D]
   float2* part_ml; // [seq][hq][split]
@@ -30,6 +31,11 @@ struct DecodeArgs {
   int max_seq_len;  // upper bound from the caller (<= 0: unknown)
   int eff_splits;   // fp8 kernel: splits that actually get work (<= num_splits; the others write empty partials)
 };
+
+// one fp32 value -> e4m3 byte, round-to-nearest-even, saturating (scaled_fp8_conversion, fp8/common.cuh:57-76)
+__device__ __forceinline__ uint8_t to_e4m3_sat(float x) {
+  return (uint8_t)__nv_cvt_float_to_fp8(fmaxf(-448.f, fminf(x, 448.f)), __NV_SATFINITE, __NV_E4M3);
+}
 
 __device__ __forceinline__ float fast_tanh(float x) {
   float y;

@@ -82,6 +82,14 @@ __global__ void __launch_bounds__(kArThreads) peer_all_reduce_oneshot_kernel(con
   const uint32_t epoch = *my_epoch + 1;
   ar_barrier(s_pads, rank, a.world, 0, epoch, a.spin_limit);
   const int64_t vec_total = a.numel / 8;
+  if (a.mc) {
+    // NVLS: the switch adds the ranks' copies (fp32 accumulation) and hands back the rounded sum
+    for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < vec_total; v += (int64_t)gridDim.x * blockDim.x)
+      reinterpret_cast<uint4*>(out)[v] = multimem_ld_reduce_add<T>(reinterpret_cast<const uint4*>(a.mc) + v);
+    __syncthreads();
+    if (threadIdx.x == 0) *my_epoch = epoch;
+    return;
+  }
   for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < vec_total; v += (int64_t)gridDim.x * blockDim.x) {
     uint4 in[kArMaxWorld];
 #pragma unroll
@@ -120,7 +128,7 @@ extern "C" void b200_peer_set_barrier_timeout(unsigned long long max_polls) {
 
 static int peer_all_reduce_impl(void* out, const uint64_t* peer_buffers, const uint64_t* peer_signal_pads, int rank,
                                 int world_size, int64_t numel, int dtype, int64_t byte_offset,
-                                int64_t signal_pad_bytes, b200_stream_t stream) {
+                                int64_t signal_pad_bytes, b200_stream_t stream, uint64_t multicast_ptr = 0) {
   using namespace b200;
   B200_CHECK_ARG(peer_buffers && peer_signal_pads, B200_ERR_INVALID_ARG, "peer_all_reduce: null pointer table");
   const bool emu = rank == -1;  // single-GPU emulation of all ranks (see include/b200_vllm.h)
@@ -152,6 +160,7 @@ static int peer_all_reduce_impl(void* out, const uint64_t* peer_buffers, const u
   a.spin_limit = ar_spin_limit();
   a.emu = emu ? 1 : 0;
   a.emu_stride = numel;
+  a.mc = (multicast_ptr && out && !emu) ? reinterpret_cast<const void*>(multicast_ptr + byte_offset) : nullptr;
   cudaStream_t s = (cudaStream_t)stream;
   const dim3 g(grid, emu ? world_size : 1);
   if (out) {
@@ -185,4 +194,14 @@ extern "C" int b200_peer_all_reduce_out(void* out, const uint64_t* peer_buffers,
   B200_CHECK_ARG(out != nullptr, B200_ERR_INVALID_ARG, "peer_all_reduce_out: null output");
   return peer_all_reduce_impl(out, peer_buffers, peer_signal_pads, rank, world_size, numel, dtype, byte_offset,
                               signal_pad_bytes, stream);
+}
+
+extern "C" int b200_nvls_all_reduce_out(void* out, uint64_t multicast_ptr, const uint64_t* peer_buffers,
+                                        const uint64_t* peer_signal_pads, int rank, int world_size, int64_t numel,
+                                        int dtype, int64_t byte_offset, int64_t signal_pad_bytes, b200_stream_t stream) {
+  B200_CHECK_ARG(out != nullptr && multicast_ptr != 0, B200_ERR_INVALID_ARG,
+                 "nvls_all_reduce_out: null output or no multicast mapping (NVLS unavailable)");
+  B200_CHECK_ARG((multicast_ptr + byte_offset) % 16 == 0, B200_ERR_ALIGNMENT, "nvls_all_reduce_out: multicast address must be 16-byte aligned");
+  return peer_all_reduce_impl(out, peer_buffers, peer_signal_pads, rank, world_size, numel, dtype, byte_offset,
+                              signal_pad_bytes, stream, multicast_ptr);
 }

@@ -46,6 +46,26 @@ __device__ __forceinline__ void ar_barrier(uint32_t* const* pads, int rank, int 
   __syncthreads();
 }
 
+// In-switch reduction (NVLS): one load returns the SUM over all ranks' copies of 8 consecutive 16-bit values,
+// accumulated in fp32 inside the NVSwitch and rounded once to T.  `mc` is the multicast address.
+template <typename T> __device__ __forceinline__ uint4 multimem_ld_reduce_add(const void* mc);
+template <> __device__ __forceinline__ uint4 multimem_ld_reduce_add<__nv_bfloat16>(const void* mc) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+template <> __device__ __forceinline__ uint4 multimem_ld_reduce_add<__half>(const void* mc) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+
 struct ArArgs;
 __device__ __forceinline__ int ar_rank(const ArArgs& a);
 
@@ -58,6 +78,7 @@ struct ArArgs {
   // Single-GPU emulation of `world` ranks (tests on a 1-GPU box): ONE cooperative launch with gridDim.y = world,
   // rank = blockIdx.y, every "rank's" buffer / signal pad on the same device; per-rank outputs are `emu_stride`
   // elements apart.  0 in production.
+  const void* mc;  // NVLS multicast mapping of the buffers (torch symmetric memory multicast_ptr + offset) or null
   int emu;
   int64_t emu_stride;
 };

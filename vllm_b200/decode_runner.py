@@ -201,7 +201,9 @@ class DecodeRunner:
             return self._all_reduce(self._mm_fp8(xq, xs, lw))
         out = self.par.view(which, self.B, self.s.hidden)
         self._mm_fp8(xq, xs, lw, out=out)
-        if self.tp <= 4:  # one-shot: (tp-1) MB of peer reads beat a second cross-GPU barrier; o/down alternate buffers
+        # one-shot (start barrier only; o/down alternate buffers): NVLS in-switch sum at any TP when the fabric has
+        # multicast, else (tp-1) MB of peer reads, which beat a second cross-GPU barrier up to TP 4
+        if self.tp <= 4 or self.par.multicast_ptr:
             return self.par.all_reduce_out(which, torch.empty_like(out))
         self.par.all_reduce_(which)
         return out
@@ -215,7 +217,7 @@ class DecodeRunner:
         # TP <= 4: the all-reduce after a row-parallel GEMM is fused with the residual add + RMSNorm + FP8 quant
         # that follows it (b200_peer_all_reduce_rms_norm_quant); `pending` = the down_proj partial sums of the
         # previous layer still sit un-reduced in peer buffer 1
-        fuse_ar = fused and self.par is not None and self.tp <= 4
+        fuse_ar = fused and self.par is not None and (self.tp <= 4 or bool(self.par.multicast_ptr))
         pending = False
         for lw, kv in zip(self.layers, self.kv_caches):
             kc, vc = kv.unbind(0)

@@ -13,6 +13,7 @@ kernel object; `plugin.register()` puts them FIRST for PlatformEnum.CUDA
 """
 from __future__ import annotations
 
+import os
 from collections.abc import Sequence
 
 import torch
@@ -30,6 +31,7 @@ from . import torch_ops  # noqa: F401  (defines torch.ops.b200.*)
 # kernel classes go through the torch.ops.b200.* custom ops (opaque, mutation-annotated, with fake impls),
 # exactly like the reference's classes go through torch.ops._C.*.
 _B = torch.ops.b200
+_OWN_QUANT = os.environ.get("B200_VLLM_QUANT", "vllm") == "b200"
 
 
 def _is_sm100(compute_capability: int | None) -> tuple[bool, str | None]:
@@ -85,6 +87,13 @@ class B200FP8ScaledMMLinearKernel(FP8ScaledMMLinearKernel):
             raise ValueError(f"B200 FP8 GEMM needs K and N to be multiples of 16, got {tuple(w.shape)}")
 
     def apply_weights(self, layer: torch.nn.Module, x: torch.Tensor, bias: torch.Tensor | None = None) -> torch.Tensor:
+        """Default: the base class's path, exactly what CutlassFP8ScaledMMLinearKernel does (ScaledMMLinearKernel.py
+        :120-160) - the activation quant stays vLLM's `QuantFP8`, which under torch.compile is plain torch ops that
+        Inductor FUSES into the preceding RMSNorm / SiLU kernel; only the GEMM is replaced.  Measured inside vLLM on
+        B200 (profiles/r02_vllm_onoff.md): quantising through our opaque custom op instead cost 4 extra launches of
+        7-10 us per layer.  B200_VLLM_QUANT=b200 selects our own quant kernels (torch.ops.b200.*_scaled_fp8_quant)."""
+        if not _OWN_QUANT:
+            return super().apply_weights(layer, x, bias)
         w, w_s, x_s, x_s_ub = self._get_layer_params(layer)
         x2 = x.reshape(-1, x.shape[-1])
         out_dtype = self.config.out_dtype or x.dtype

@@ -160,12 +160,21 @@ def paged_attention_decode(
     logits_soft_cap: float = 0.0,
     sliding_window: int = 0,
     token_to_seq: torch.Tensor | None = None,
+    output_scale: torch.Tensor | None = None,
 ) -> torch.Tensor:
     """One query token per sequence (or, with token_to_seq int32 [S], one per query token of a
     mixed batch: row s reads block_table[token_to_seq[s]] with causal length seq_lens[s]).  query/out [S, Hq, D]; caches are 4-D views
     (num_blocks, block_size, Hkv, D) with any strides; block_table int32 [S, max_blocks];
-    seq_lens int32 [S].  fp8 caches are uint8 / float8 storage + per-tensor k/v scales."""
-    _require_cuda(out, query, key_cache, value_cache, block_table, seq_lens)
+    seq_lens int32 [S].  fp8 caches are uint8 / float8 storage + per-tensor k/v scales.
+    output_scale (fp32 [1], optional): fused static FP8 output quant - `out` must then be a float8_e4m3fn / uint8
+    tensor of query's shape and receives e4m3(o / output_scale) (AttentionImpl.forward(output_scale=...))."""
+    _require_cuda(out, query, key_cache, value_cache, block_table, seq_lens, output_scale)
+    if output_scale is not None:
+        if out.element_size() != 1 or output_scale.numel() != 1 or output_scale.dtype != torch.float32:
+            raise RuntimeError("paged_attention_decode: output_scale needs a 1-byte (float8_e4m3fn) out tensor and a "
+                               "float32 scale with one element")
+    elif out.dtype != query.dtype:
+        raise RuntimeError("paged_attention_decode: out must have the query dtype (or pass output_scale for fp8 output)")
     if query.dim() != 3 or out.shape != query.shape:
         raise RuntimeError("paged_attention_decode: query/out must be [num_seqs, num_heads, head_size]")
     if key_cache.dim() != 4 or value_cache.dim() != 4:
@@ -206,7 +215,7 @@ def paged_attention_decode(
         num_seqs=num_seqs, num_q_heads=num_q_heads, num_kv_heads=num_kv_heads, head_size=head_size,
         block_size=block_size, max_seq_len=int(max_seq_len), q_dtype=_dt(query), kv_dtype=kv,
         num_splits=int(num_splits), scale=float(scale), logits_soft_cap=float(logits_soft_cap),
-        sliding_window=int(sliding_window))
+        sliding_window=int(sliding_window), output_scale=_ptr(output_scale))
     rc = _lib.load().b200_paged_attention_decode(C.byref(p), _stream(query))
     _lib.check(rc, "paged_attention_decode")
     return out

@@ -9,6 +9,7 @@ same view - no staging copies.  Mirrors what the reference's `CustomAllreduce`
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.distributed as dist
@@ -35,6 +36,15 @@ class PeerAllReduce:
         self._bufs = (C.c_uint64 * self.world)(*bufs)
         self._pads = (C.c_uint64 * self.world)(*pads)
         self._pad_bytes = int(self.handle.signal_pad_size)
+        # NVLS: the multicast mapping of the same allocation (0 = no multicast support on this fabric / disabled)
+        mc = 0
+        if os.environ.get("B200_NVLS", "1") != "0":
+            try:
+                if getattr(self.handle, "has_multicast_support", lambda *a: True) and int(self.handle.multicast_ptr):
+                    mc = int(self.handle.multicast_ptr)
+            except Exception:  # noqa: BLE001 - older torch builds have no multicast_ptr
+                mc = 0
+        self.multicast_ptr = mc
         self._dt = 2 if dtype == torch.bfloat16 else 1  # B200_DT_BF16 / B200_DT_F16
         torch.cuda.synchronize(device)
         dist.barrier(group)
@@ -55,6 +65,12 @@ class PeerAllReduce:
 
         if out.numel() != self.numel or out.dtype != self.dtype or not out.is_contiguous():
             raise RuntimeError("PeerAllReduce.all_reduce_out: out must be a contiguous tensor of the buffer's size/dtype")
+        if self.multicast_ptr:
+            rc = _lib.load().b200_nvls_all_reduce_out(out.data_ptr(), self.multicast_ptr, self._bufs, self._pads, self.rank,
+                                                      self.world, self.numel, self._dt, index * self.numel * 2,
+                                                      self._pad_bytes, _stream(self.storage))
+            _lib.check(rc, "nvls_all_reduce_out")
+            return out
         rc = _lib.load().b200_peer_all_reduce_out(out.data_ptr(), self._bufs, self._pads, self.rank, self.world,
                                                   self.numel, self._dt, index * self.numel * 2, self._pad_bytes,
                                                   _stream(self.storage))
@@ -72,6 +88,13 @@ class PeerAllReduce:
             raise RuntimeError("PeerAllReduce.all_reduce_rms_norm_quant: shapes do not match the buffer")
         xq = torch.empty(num_tokens, hidden, dtype=torch.float8_e4m3fn, device=residual.device)
         xs = torch.empty(num_tokens, 1, dtype=torch.float32, device=residual.device)
+        if self.multicast_ptr:
+            rc = _lib.load().b200_nvls_all_reduce_rms_norm_quant(
+                xq.data_ptr(), xs.data_ptr(), self.multicast_ptr, self._bufs, self._pads, self.rank, self.world,
+                index * self.numel * 2, self._pad_bytes, weight.data_ptr(), residual.data_ptr(), float(epsilon),
+                num_tokens, hidden, self._dt, _stream(self.storage))
+            _lib.check(rc, "nvls_all_reduce_rms_norm_quant")
+            return xq, xs
         rc = _lib.load().b200_peer_all_reduce_rms_norm_quant(
             xq.data_ptr(), xs.data_ptr(), self._bufs, self._pads, self.rank, self.world, index * self.numel * 2,
             self._pad_bytes, weight.data_ptr(), residual.data_ptr(), float(epsilon), num_tokens, hidden, self._dt,

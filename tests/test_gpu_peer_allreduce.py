@@ -106,7 +106,7 @@ def test_emulated_all_reduce_rms_norm_quant(cuda_lib, world):
 
 # ------------------------------------------------------------------------------- real ranks
 def _worker(rank, world, port, q, nvls):
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), B200_NVLS="1" if nvls else "0")
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), B200_NVLS="force" if nvls else "0")
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)

@@ -258,7 +258,10 @@ def test_nvfp4_quant_golden_and_padded(ops):
 @pytest.mark.parametrize("mnk", [(128, 128, 64), (150, 128, 64), (128, 128, 96), (16, 256, 512), (1, 7168, 8192),
                                  (256, 1280, 8192), (64, 8192, 1024), (300, 2048, 3584), (129, 160, 160),
                                  # decode regime, cluster split-K over DSMEM (S = 8, 2, 4, 8, 3) incl. ragged token counts
-                                 (200, 1280, 8192), (256, 8192, 3584), (100, 384, 2048), (17, 128, 4096), (250, 256, 1536)])
+                                 (200, 1280, 8192), (256, 8192, 3584), (100, 384, 2048), (17, 128, 4096), (250, 256, 1536),
+                                 # persistent 2-CTA kernel (M > 256): wide (BN 256, one accumulator) and narrow (BN 128, two)
+                                 # tiles, several tiles per cluster, ragged M / N / K
+                                 (1024, 2048, 4096), (2048, 7168, 1024), (700, 1280, 2112), (4096, 8192, 512), (513, 160, 96)])
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 def test_nvfp4_gemm(ops, mnk, dtype):
     M, N, K = mnk

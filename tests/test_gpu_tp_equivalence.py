@@ -18,9 +18,12 @@ if str(ROOT) not in sys.path:
 
 pytestmark = pytest.mark.gpu
 
-# activations are re-quantised to fp8 per token on every rank's shard: e4m3 has 3 mantissa bits (2^-4 relative
-# rounding), averaged over a 1024-wide row that is ~1-2 % of the hidden state's norm after 2 layers
-REL_L2_BOUND = 0.05
+# What differs between TP=N and TP=1 on the same weights: the row-parallel partial sums are rounded to bf16 before
+# the all-reduce and added in another order, and every difference passes through the next linear's activation
+# quantiser (fp8 per-token dynamic / 4-bit NVFP4 blocks), which amplifies it.  Measured on 2 x B200 after 2 layers:
+# 0.041 (fp8) and 0.094 (nvfp4) relative L2, 87.5 % equal greedy tokens.  A sharding mistake (wrong head / column
+# slice) gives ~1.4 (uncorrelated vectors) and ~0 equal tokens.
+REL_L2_BOUND = {"fp8": 0.10, "nvfp4": 0.25}
 
 
 def _worker(rank, world, port, q, wq):
@@ -58,7 +61,7 @@ def test_tp_step_matches_tp1(world, wq):
         p.join(timeout=60)
     print(allres)
     for r in allres:
-        assert r["hidden_rel_l2"] < REL_L2_BOUND, r
+        assert r["hidden_rel_l2"] < REL_L2_BOUND[wq], r
         assert r["tokens_equal_frac"] >= 0.5, r  # near-ties of random logits flip under 1-2 % noise; a sharding bug gives ~1/8192
     # every rank holds the same reduced hidden state
     assert len({round(r["hidden_rel_l2"], 9) for r in allres}) == 1, allres

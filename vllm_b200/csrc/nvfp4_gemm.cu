@@ -365,6 +365,11 @@ static int launch_f4(const CUtensorMap& tx, const CUtensorMap& ty, const F4Args&
   return 0;
 }
 
+// large M: persistent 2-CTA kernel (gemm_persist.cu); returns 1 when it does not take the shape
+template <typename OutT>
+int run_nvfp4_gemm_2sm(void* out, const void* a, const void* b, const void* sfa, const void* sfb, const float* alpha,
+                       int M, int N, int K, int64_t ldc, cudaStream_t stream);
+
 template <typename OutT>
 static int run_f4(void* out, const void* a, const void* b, const void* sfa, const void* sfb, const float* alpha,
                   int M, int N, int K, int64_t ldc, cudaStream_t stream) {
@@ -423,6 +428,14 @@ static int run_f4(void* out, const void* a, const void* b, const void* sfa, cons
     });
     g.splits = S;
     return dispatch(dim3(tiles * S, 1, 1), nullptr);
+  }
+  static const bool use_2sm = [] {
+    const char* e = getenv("B200_F4_2SM");  // tuning aid: 0 = the one-tile-per-CTA kernel below
+    return !(e && *e && atoi(e) == 0);
+  }();
+  if (use_2sm && M > 256) {
+    const int r2 = run_nvfp4_gemm_2sm<OutT>(out, a, b, sfa, sfb, alpha, M, N, K, ldc, stream);
+    if (r2 <= 0) return r2;
   }
   g.sfx = reinterpret_cast<const uint8_t*>(sfa);
   g.sfy = reinterpret_cast<const uint8_t*>(sfb);

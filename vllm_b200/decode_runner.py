@@ -55,11 +55,14 @@ class DecodeRunner:
     def __init__(self, shape: ModelShape, batch: int, max_ctx: int, *, block_size: int = 16,
                  kv_cache_dtype: str = "fp8", weight_quant: str = "fp8", tp_size: int = 1, tp_rank: int = 0,
                  device: torch.device | str = "cuda:0", seed: int = 0, num_layers: int | None = None,
-                 tp_group=None, fused: bool = True):
+                 tp_group=None, fused: bool = True, skip_collectives: bool = False):
         self.s = shape
         self.B, self.max_ctx, self.bs = batch, max_ctx, block_size
         self.kv_dtype, self.wq = kv_cache_dtype, weight_quant
         self.tp, self.rank, self.group = tp_size, tp_rank, tp_group
+        # development aid: run ONE rank's shard of a TP=N model on a single GPU with every collective skipped (the sums
+        # are wrong, the per-rank kernels and their cost are exactly those of the N-GPU step minus the all-reduces)
+        self.skip_collectives = skip_collectives
         self.fused = fused  # use the fused norm+quant / silu+quant / rope+cache kernels
         self.dev = torch.device(device)
         self.L = num_layers if num_layers is not None else shape.num_layers
@@ -141,7 +144,7 @@ class DecodeRunner:
         # Row-parallel partial sums: two-shot all-reduce over NVLink peer memory (b200_peer_all_reduce) on
         # symmetric buffers the o_proj / down_proj GEMMs write into; NCCL when that cannot be set up.
         self.par = None
-        if tp_size > 1 and self.wq == "fp8" and os.environ.get("B200_PEER_ALLREDUCE", "1") != "0":
+        if tp_size > 1 and not skip_collectives and os.environ.get("B200_PEER_ALLREDUCE", "1") != "0":
             try:
                 from .peer_comm import PeerAllReduce
 
@@ -162,19 +165,31 @@ class DecodeRunner:
         q, sf = ops.scaled_fp4_quant(shard(w).contiguous(), gs)  # 16-element blocks never straddle a shard boundary
         return {"w": q, "sf": sf, "gs": gs}
 
-    def _linear(self, x: torch.Tensor, lw) -> torch.Tensor:
+    def _linear(self, x: torch.Tensor, lw, out: torch.Tensor | None = None) -> torch.Tensor:
         if self.wq == "fp8":
             xq, xs = ops.scaled_fp8_quant(x, use_per_token_if_dynamic=True)
-            return ops.cutlass_scaled_mm(xq, lw["w"].t(), xs, lw["s"], self.dtype)
+            return ops.cutlass_scaled_mm(xq, lw["w"].t(), xs, lw["s"], self.dtype, out=out)
         # NVFP4: static activation global scale (ModelOpt input_scale), here a fixed calibration constant
         if "ags" not in lw:
             lw["ags"] = torch.tensor([448.0 * 6.0 / 8.0], device=self.dev)
             lw["alpha"] = (1.0 / (lw["ags"] * lw["gs"])).float()
         xq, xsf = ops.scaled_fp4_quant(x, lw["ags"])
-        return ops.cutlass_scaled_fp4_mm(xq, lw["w"], xsf, lw["sf"], lw["alpha"], self.dtype)
+        return ops.cutlass_scaled_fp4_mm(xq, lw["w"], xsf, lw["sf"], lw["alpha"], self.dtype, out=out)
+
+    def _row_parallel(self, x: torch.Tensor, lw, which: int) -> torch.Tensor:
+        """Row-parallel linear (quant + GEMM, either weight format) + sum over the ranks; the GEMM writes its
+        partial sums straight into the symmetric buffer `which` (o_proj: 0, down_proj: 1)."""
+        if self.par is None:
+            return self._all_reduce(self._linear(x, lw))
+        out = self.par.view(which, self.B, self.s.hidden)
+        self._linear(x, lw, out=out)
+        if self.tp <= 4 or self.par.multicast_ptr:
+            return self.par.all_reduce_out(which, torch.empty_like(out))
+        self.par.all_reduce_(which)
+        return out
 
     def _all_reduce(self, x: torch.Tensor) -> torch.Tensor:
-        if self.tp > 1:
+        if self.tp > 1 and not self.skip_collectives:
             dist.all_reduce(x, group=self.group)
         return x
 
@@ -255,7 +270,7 @@ class DecodeRunner:
                 oq, o_s = ops.scaled_fp8_quant(attn_out.view(B, -1), use_per_token_if_dynamic=True)
                 hidden = self._row_parallel_fp8(oq, o_s, lw["o"], 0)
             else:
-                hidden = self._all_reduce(self._linear(attn_out.view(B, -1), lw["o"]))
+                hidden = self._row_parallel(attn_out.view(B, -1), lw["o"], 0)
             if fused:
                 xq, xs = ops.rms_norm_dynamic_per_token_quant(hidden, lw["ln2"], s.rms_eps, residual=residual)
                 gu = self._mm_fp8(xq, xs, lw["gate_up"])
@@ -266,13 +281,13 @@ class DecodeRunner:
                 gu = self._linear(hidden, lw["gate_up"])
                 act = torch.empty(B, self.inter, device=self.dev, dtype=self.dtype)
                 ops.silu_and_mul(act, gu)
-                hidden = self._all_reduce(self._linear(act, lw["down"]))
+                hidden = self._row_parallel(act, lw["down"], 1)
         if pending:  # the last layer's down_proj: plain one-shot all-reduce, then the final norm
             hidden = self.par.all_reduce_out(1, torch.empty(B, s.hidden, device=self.dev, dtype=self.dtype))
         ops.fused_add_rms_norm(hidden, residual, self.final_ln, s.rms_eps)
         self.last_hidden = hidden  # [B, hidden] after the final norm (TP-equivalence checks read it)
         logits = torch.matmul(hidden, self.lm_head.t())  # plain library GEMM (bf16 lm_head, as in vLLM)
-        if self.tp == 1:
+        if self.tp == 1 or self.skip_collectives:
             self.next_tokens.copy_(logits.argmax(-1))
         else:
             mx, idx = logits.float().max(-1)

@@ -244,6 +244,21 @@ int b200_scaled_fp4_quant(void* output, void* output_sf, const void* input,
                           int out_n, int swizzled, int dtype,
                           b200_stream_t stream);
 
+/* Fused NVFP4 activation producers: the quantiser above with its producer folded in, always with the
+ * swizzled tensor-core scale layout (every padded scale written as 0).
+ *   b200_silu_and_mul_nvfp4_quant  input [m][2d] = [gate | up]; quantises T(silu(gate) * up), the product formed in
+ *     fp32 and rounded to T once.  Replaces: silu_and_mul_nvfp4_quant
+ *       csrc/libtorch_stable/quantization/fp4/activation_nvfp4_quant_fusion_kernels.cu:39-113 (+ launcher),
+ *       math nvfp4_utils.cuh:304-329, schema csrc/libtorch_stable/torch_bindings.cpp:251-253.
+ *   b200_rms_norm_nvfp4_quant      (residual += input;) quantises RMSNorm(.) * weight.  The reference has no such
+ *     kernel (its NVFP4 path runs fused_add_rms_norm, csrc/layernorm_kernels.cu, then scaled_fp4_quant); this is
+ *     bit-identical to b200_rms_norm followed by b200_scaled_fp4_quant.  residual may be NULL. */
+int b200_silu_and_mul_nvfp4_quant(void* result, void* result_block_scale, const void* input,
+                                  const float* input_global_scale, int m, int d, int dtype, b200_stream_t stream);
+int b200_rms_norm_nvfp4_quant(void* result, void* result_block_scale, const void* input, const void* weight,
+                              void* residual, const float* input_global_scale, int m, int hidden,
+                              int64_t in_row_stride, float epsilon, int dtype, b200_stream_t stream);
+
 /* ------------------------------------------------------------------------
  * FP8 W8A8 GEMM (tcgen05 / TMEM / TMA).
  * Replaces: cutlass_scaled_mm
@@ -380,13 +395,22 @@ int b200_peer_all_reduce_rms_norm_quant(void* result, float* scales, const uint6
                                         void* residual, float epsilon, int64_t num_tokens, int hidden, int dtype,
                                         b200_stream_t stream);
 
-/* NVLS variants (in-switch reduction): the same two operations with ONE `multimem.ld_reduce` per 16 bytes instead
- * of world_size peer loads - the NVSwitch adds the ranks' copies with fp32 accumulation and returns the sum rounded
- * once to the element type.  multicast_ptr = the multicast mapping of the same symmetric allocation
+/* NVLS variants (in-switch reduction): ONE `multimem.ld_reduce` per 16 bytes instead of world_size peer loads -
+ * the NVSwitch adds the ranks' copies with fp32 accumulation and returns the sum rounded once to the element type.
+ *   b200_nvls_all_reduce                 in place, TWO-shot through the switch: rank r reduces slice r and writes it
+ *                                        back with one multicast store (`multimem.st`) that the switch replicates to
+ *                                        every rank; per-GPU link traffic ~ the message size whatever the world size.
+ *   b200_nvls_all_reduce_out             one-shot into a local `out` (every rank reduces the whole message).
+ *   b200_nvls_all_reduce_rms_norm_quant  two-shot per CTA (each CTA owns rows: reduce + multicast its column slice,
+ *                                        second barrier, then residual add + RMSNorm + FP8 quant on the local rows);
+ *                                        hidden % (8 * world_size) == 0.  The summed GEMM output is left in the buffer.  multicast_ptr = the multicast mapping of the same symmetric allocation
  * (torch.distributed._symmetric_memory handle.multicast_ptr; 0 when the fabric has no multicast support -> error).
  * Reference analogue: vllm/distributed/device_communicators/symm_mem.py:137-150 (torch.ops.symm_mem.
  * multimem_all_reduce_) and the fused AR+RMSNorm of flashinfer_all_reduce.py.  Same call-order and
  * buffer-alternation rules as the peer-load entries; world sizes 2..8, incl. the fused form at 8 ranks. */
+int b200_nvls_all_reduce(uint64_t multicast_ptr, const uint64_t* peer_buffers, const uint64_t* peer_signal_pads,
+                         int rank, int world_size, int64_t numel, int dtype, int64_t byte_offset,
+                         int64_t signal_pad_bytes, b200_stream_t stream);
 int b200_nvls_all_reduce_out(void* out, uint64_t multicast_ptr, const uint64_t* peer_buffers,
                              const uint64_t* peer_signal_pads, int rank, int world_size, int64_t numel,
                              int dtype, int64_t byte_offset, int64_t signal_pad_bytes, b200_stream_t stream);

@@ -365,6 +365,65 @@ def test_fused_silu_mul_fp8_quant_is_the_composition(ops, shape):
     torch.testing.assert_close(s.cpu(), rs, rtol=1e-2, atol=0)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape", [(256, 3584), (128, 14336), (7, 48), (130, 80), (1, 16)])
+def test_silu_and_mul_nvfp4_quant(ops, shape, dtype):
+    """silu_and_mul_nvfp4_quant: (a) bit-exact against the reference's own fused CUDA kernel when the installed
+    wheel has it; (b) against our quantiser applied to T(silu(g) * u) formed in fp32 by torch - the kernel uses the
+    reference's __expf / __fdividef, so an element can round to the neighbouring T value: >= 99.5 % of the codes and
+    of the scale bytes agree, and every padded scale byte is written."""
+    M, d = shape
+    g = torch.Generator().manual_seed(d + M)
+    gu = (torch.randn(M, 2 * d, generator=g) * 2).to(dtype).to(DEV)
+    gs = torch.tensor([448.0 * 6.0 / 12.0], device=DEV)
+    out = torch.empty(M, d // 2, dtype=torch.uint8, device=DEV)
+    sf = torch.full(((M + 127) // 128 * 128, (d // 16 + 3) // 4), -1, dtype=torch.int32, device=DEV)
+    ops.silu_and_mul_nvfp4_quant(out, sf, gu, gs)
+    x, u = gu[:, :d].float(), gu[:, d:].float()
+    act = ((x / (1.0 + torch.exp(-x))) * u).to(dtype)
+    out2, sf2 = ops.scaled_fp4_quant(act, gs)
+    same_sf = (sf.view(torch.uint8) == sf2.view(torch.uint8)).float().mean().item()
+    same = (out == out2).float().mean().item()
+    assert same_sf >= 0.995 and same >= 0.995, (same_sf, same)
+    try:
+        import vllm._C  # noqa: F401
+        assert hasattr(torch.ops._C, "silu_and_mul_nvfp4_quant")
+    except Exception:  # pragma: no cover
+        return
+    ref_out = torch.empty_like(out)
+    ref_sf = torch.zeros_like(sf)
+    torch.ops._C.silu_and_mul_nvfp4_quant(ref_out, ref_sf, gu, gs)
+    assert torch.equal(out, ref_out), f"codes differ from the reference's fused kernel for {shape} {dtype}"
+    # the reference leaves the padding of the scale buffer untouched (zeros here); ours writes zeros
+    assert torch.equal(sf.view(torch.uint8), ref_sf.view(torch.uint8))
+
+
+@pytest.mark.parametrize("with_res", [True, False])
+@pytest.mark.parametrize("shape", [(256, 8192), (128, 4096), (5, 80), (130, 1024)])
+def test_rms_norm_nvfp4_quant_is_the_composition(ops, shape, with_res):
+    """One kernel == b200_rms_norm (fused add) followed by b200_scaled_fp4_quant, bit for bit, residual included."""
+    M, H = shape
+    g = torch.Generator().manual_seed(H + M)
+    x = torch.randn(M, H, generator=g).to(torch.bfloat16).to(DEV)
+    w = (torch.rand(H, generator=g) + 0.5).to(torch.bfloat16).to(DEV)
+    res = torch.randn(M, H, generator=g).to(torch.bfloat16).to(DEV) if with_res else None
+    gs = torch.tensor([448.0 * 6.0 / 8.0], device=DEV)
+    r1 = res.clone() if with_res else None
+    out, sf = ops.rms_norm_nvfp4_quant(x, w, 1e-5, gs, residual=r1,
+                                       result_block_scale=torch.full(((M + 127) // 128 * 128, (H // 16 + 3) // 4), -1,
+                                                                     dtype=torch.int32, device=DEV))
+    if with_res:
+        x2, r2 = x.clone(), res.clone()
+        ops.fused_add_rms_norm(x2, r2, w, 1e-5)
+        assert torch.equal(r1, r2)
+    else:
+        x2 = torch.empty_like(x)
+        ops.rms_norm(x2, x, w, 1e-5)
+    out2, sf2 = ops.scaled_fp4_quant(x2, gs)
+    assert torch.equal(sf.view(torch.uint8), sf2.view(torch.uint8))
+    assert torch.equal(out, out2)
+
+
 @pytest.mark.parametrize("kv_dtype", ["auto", "fp8"])
 def test_fused_rope_cache_write_is_the_composition(ops, kv_dtype):
     T, Hq, Hkv, D, bs, nb = 37, 32, 8, 128, 16, 40

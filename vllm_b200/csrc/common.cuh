@@ -145,18 +145,32 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug traps instead of hanging the GPU box.
+// Bounded wait: a protocol bug traps instead of hanging the GPU box.  The bound is WALL TIME (%globaltimer, read
+// once per 2^20 polls), not a poll count: a kernel launched with programmatic dependent launch legitimately sits in
+// its first wait for as long as its predecessor runs, and the predecessor may be an all-reduce waiting for a rank
+// that is seconds behind (capturing a graph, starting a profiler - seen at TP8).
+constexpr unsigned long long kMbarTimeoutNs = 120ull * 1000000000ull;
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 #ifdef B200_UNBOUNDED_WAIT
   while (!mbar_try_wait(bar, parity)) {
   }
 #else
   uint32_t spins = 0;
+  unsigned long long t0 = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > (1u << 22)) {
-      printf("b200: mbarrier wait timed out (block %d,%d,%d thread %d parity %u, barrier at shared 0x%x)\n", blockIdx.x,
-             blockIdx.y, blockIdx.z, threadIdx.x, parity, smem_u32(bar));
-      __trap();
+    if ((++spins & 0xFFFFFu) == 0) {
+      const unsigned long long now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > kMbarTimeoutNs) {
+        printf("b200: mbarrier wait timed out (block %d,%d,%d thread %d parity %u, barrier at shared 0x%x)\n",
+               blockIdx.x, blockIdx.y, blockIdx.z, threadIdx.x, parity, smem_u32(bar));
+        __trap();
+      }
     }
   }
 #endif

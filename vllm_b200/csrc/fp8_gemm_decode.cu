@@ -109,6 +109,7 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta) 
 }
 __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity) {
   uint32_t ok = 0, spins = 0;
+  unsigned long long t0 = 0;  // wall-time bound, see mbar_wait (common.cuh)
   while (!ok) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -117,9 +118,13 @@ __device__ __forceinline__ void mbar_wait_cluster(uint64_t* bar, uint32_t parity
         : "=r"(ok)
         : "r"(smem_u32(bar)), "r"(parity)
         : "memory");
-    if (!ok && ++spins > (1u << 22)) {
-      printf("b200: cluster mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
-      __trap();
+    if (!ok && (++spins & 0xFFFFFu) == 0) {
+      const unsigned long long now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > kMbarTimeoutNs) {
+        printf("b200: cluster mbarrier wait timed out (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+        __trap();
+      }
     }
   }
 }

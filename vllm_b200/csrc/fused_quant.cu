@@ -165,14 +165,29 @@ __global__ void __launch_bounds__(1024) peer_allreduce_rms_norm_quant_kernel(
   const uint32_t epoch = *my_epoch + 1;
   ar_barrier(s_pads, rank, a.world, 0, epoch, a.spin_limit);
   const int nv = hidden / N;
+  if (a.mc) {
+    // NVLS, two-shot per CTA: of THIS CTA's rows, rank r asks the switch for the sum of column slice r
+    // (multimem.ld_reduce, fp32 accumulation, rounded to T once) and multicasts it into every rank's buffer; after
+    // the second barrier (same CTA index on every rank = same rows) the whole rows are in the local buffer.
+    const int cpr = nv / a.world;  // 16-byte vectors of one row per rank (host: hidden % (8 * world) == 0)
+    const int my_rows = (num_tokens - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    uint4* mc = reinterpret_cast<uint4*>(const_cast<void*>(a.mc));
+    for (int i = threadIdx.x; i < my_rows * cpr; i += blockDim.x) {
+      const int k = i / cpr, c = i - k * cpr;
+      const int64_t idx = (int64_t)(blockIdx.x + k * gridDim.x) * nv + rank * cpr + c;
+      const uint4 sum = multimem_ld_reduce_add<T>(mc + idx);
+      multimem_st<T>(mc + idx, sum);
+    }
+    ar_barrier(s_pads, rank, a.world, 1, epoch, a.spin_limit);
+  }
   for (int row = blockIdx.x; row < num_tokens; row += gridDim.x) {
     T* res = residual + (int64_t)row * hidden;
     uint8_t* dst = out + (int64_t)row * hidden;
     float ss = 0.f;
     for (int v = threadIdx.x; v < nv; v += blockDim.x) {
       float acc[N];
-      if (a.mc) {  // NVLS: in-switch sum over the ranks (fp32 accumulation, rounded to T once)
-        const uint4 sm = multimem_ld_reduce_add<T>(reinterpret_cast<const uint4*>(a.mc) + (int64_t)row * nv + v);
+      if (a.mc) {  // the summed row, multicast into the local buffer above (L2: other SMs' L1s never saw it)
+        const uint4 sm = __ldcg(reinterpret_cast<const uint4*>(a.bufs[rank]) + (int64_t)row * nv + v);
         const T* e = reinterpret_cast<const T*>(&sm);
 #pragma unroll
         for (int i = 0; i < N; ++i) acc[i] = to_float(e[i]);
@@ -537,6 +552,8 @@ static int ar_rms_norm_quant_impl(void* result, float* scales, const uint64_t* p
   a.emu = emu ? 1 : 0;
   a.emu_stride = num_tokens * hidden;
   a.mc = (multicast_ptr && !emu) ? reinterpret_cast<const void*>(multicast_ptr + byte_offset) : nullptr;
+  B200_CHECK_ARG(!a.mc || hidden % (8 * world_size) == 0, B200_ERR_INVALID_ARG,
+                 "nvls_all_reduce_rms_norm_quant: hidden must be a multiple of 8 * world_size");
   return dispatch16f(dtype, "peer_all_reduce_rms_norm_quant", [&](auto tag) {
     using T = decltype(tag);
     if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(peer_allreduce_rms_norm_quant_kernel<T>), 49152 * 4)) return rc_attr;

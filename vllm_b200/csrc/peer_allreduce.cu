@@ -115,6 +115,31 @@ __global__ void __launch_bounds__(kArThreads) peer_all_reduce_oneshot_kernel(con
   if (threadIdx.x == 0) *my_epoch = epoch;
 }
 
+// Two-shot THROUGH THE SWITCH (NVLS), in place: rank r asks the switch for the sum of slice r over all ranks
+// (multimem.ld_reduce: one 16-byte load returns 8 summed values, fp32 accumulation, rounded once) and stores it
+// with ONE multicast store that the switch replicates into every rank's buffer.  Per GPU the links carry
+// ~numel*2 bytes each way whatever the world size (the one-shot forms pull world x that), and neither the loads
+// nor the stores are issued once per peer.  Same barriers as peer_all_reduce_kernel.
+template <typename T>
+__global__ void __launch_bounds__(kArThreads) nvls_all_reduce_kernel(const ArArgs a) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ uint32_t* s_pads[kArMaxWorld];
+  if ((int)threadIdx.x < a.world) s_pads[threadIdx.x] = a.pads[threadIdx.x];
+  const int rank = a.rank;
+  uint32_t* my_epoch = a.pads[rank] + blockIdx.x * kArSlotWords + 2 * kArMaxWorld;
+  const uint32_t epoch = *my_epoch + 1;
+  ar_barrier(s_pads, rank, a.world, 0, epoch, a.spin_limit);
+  const int64_t per_rank = a.numel / 8 / a.world;
+  uint4* mc = reinterpret_cast<uint4*>(const_cast<void*>(a.mc)) + per_rank * rank;
+  for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < per_rank; v += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 sum = multimem_ld_reduce_add<T>(mc + v);
+    multimem_st<T>(mc + v, sum);
+  }
+  ar_barrier(s_pads, rank, a.world, 1, epoch, a.spin_limit);
+  if (threadIdx.x == 0) *my_epoch = epoch;
+}
+
 }  // namespace b200
 
 namespace b200 {
@@ -160,10 +185,13 @@ static int peer_all_reduce_impl(void* out, const uint64_t* peer_buffers, const u
   a.spin_limit = ar_spin_limit();
   a.emu = emu ? 1 : 0;
   a.emu_stride = numel;
-  a.mc = (multicast_ptr && out && !emu) ? reinterpret_cast<const void*>(multicast_ptr + byte_offset) : nullptr;
+  a.mc = (multicast_ptr && !emu) ? reinterpret_cast<const void*>(multicast_ptr + byte_offset) : nullptr;
   cudaStream_t s = (cudaStream_t)stream;
   const dim3 g(grid, emu ? world_size : 1);
-  if (out) {
+  if (!out && a.mc) {
+    if (dtype == B200_DT_BF16) launch_kernel_ex(nvls_all_reduce_kernel<__nv_bfloat16>, g, dim3(kArThreads), 0, s, 1, false, a);
+    else launch_kernel_ex(nvls_all_reduce_kernel<__half>, g, dim3(kArThreads), 0, s, 1, false, a);
+  } else if (out) {
     B200_CHECK_ARG(reinterpret_cast<uintptr_t>(out) % 16 == 0, B200_ERR_ALIGNMENT, "peer_all_reduce: out must be 16-byte aligned");
     if (dtype == B200_DT_BF16)
       launch_kernel_ex(peer_all_reduce_oneshot_kernel<__nv_bfloat16>, g, dim3(kArThreads), 0, s, 1, emu, a,
@@ -203,5 +231,15 @@ extern "C" int b200_nvls_all_reduce_out(void* out, uint64_t multicast_ptr, const
                  "nvls_all_reduce_out: null output or no multicast mapping (NVLS unavailable)");
   B200_CHECK_ARG((multicast_ptr + byte_offset) % 16 == 0, B200_ERR_ALIGNMENT, "nvls_all_reduce_out: multicast address must be 16-byte aligned");
   return peer_all_reduce_impl(out, peer_buffers, peer_signal_pads, rank, world_size, numel, dtype, byte_offset,
+                              signal_pad_bytes, stream, multicast_ptr);
+}
+
+extern "C" int b200_nvls_all_reduce(uint64_t multicast_ptr, const uint64_t* peer_buffers,
+                                    const uint64_t* peer_signal_pads, int rank, int world_size, int64_t numel,
+                                    int dtype, int64_t byte_offset, int64_t signal_pad_bytes, b200_stream_t stream) {
+  B200_CHECK_ARG(multicast_ptr != 0 && rank >= 0, B200_ERR_INVALID_ARG,
+                 "nvls_all_reduce: no multicast mapping (NVLS unavailable) or emulated rank");
+  B200_CHECK_ARG((multicast_ptr + byte_offset) % 16 == 0, B200_ERR_ALIGNMENT, "nvls_all_reduce: multicast address must be 16-byte aligned");
+  return peer_all_reduce_impl(nullptr, peer_buffers, peer_signal_pads, rank, world_size, numel, dtype, byte_offset,
                               signal_pad_bytes, stream, multicast_ptr);
 }

@@ -66,6 +66,19 @@ template <> __device__ __forceinline__ uint4 multimem_ld_reduce_add<__half>(cons
   return r;
 }
 
+// Multicast store: one store lands in EVERY rank's copy (the switch replicates it).
+template <typename T> __device__ __forceinline__ void multimem_st(void* mc, const uint4& v);
+template <> __device__ __forceinline__ void multimem_st<__nv_bfloat16>(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+template <> __device__ __forceinline__ void multimem_st<__half>(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f16x2 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+
 struct ArArgs;
 __device__ __forceinline__ int ar_rank(const ArArgs& a);
 

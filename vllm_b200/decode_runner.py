@@ -170,11 +170,33 @@ class DecodeRunner:
             xq, xs = ops.scaled_fp8_quant(x, use_per_token_if_dynamic=True)
             return ops.cutlass_scaled_mm(xq, lw["w"].t(), xs, lw["s"], self.dtype, out=out)
         # NVFP4: static activation global scale (ModelOpt input_scale), here a fixed calibration constant
+        self._fp4_consts(lw)
+        xq, xsf = ops.scaled_fp4_quant(x, lw["ags"])
+        return ops.cutlass_scaled_fp4_mm(xq, lw["w"], xsf, lw["sf"], lw["alpha"], self.dtype, out=out)
+
+    def _fp4_consts(self, lw) -> None:
         if "ags" not in lw:
             lw["ags"] = torch.tensor([448.0 * 6.0 / 8.0], device=self.dev)
             lw["alpha"] = (1.0 / (lw["ags"] * lw["gs"])).float()
-        xq, xsf = ops.scaled_fp4_quant(x, lw["ags"])
-        return ops.cutlass_scaled_fp4_mm(xq, lw["w"], xsf, lw["sf"], lw["alpha"], self.dtype, out=out)
+
+    def _fp4_bufs(self, m: int, k: int) -> tuple[torch.Tensor, torch.Tensor]:
+        """Packed codes + swizzled scale buffer; torch.empty: our quantisers write every padded scale themselves."""
+        return (torch.empty(m, k // 2, dtype=torch.uint8, device=self.dev),
+                torch.empty(ops.round_up(m, 128), ops.round_up(k // 16, 4) // 4, dtype=torch.int32, device=self.dev))
+
+    def _mm_fp4(self, xq: torch.Tensor, xsf: torch.Tensor, lw, out: torch.Tensor | None = None) -> torch.Tensor:
+        return ops.cutlass_scaled_fp4_mm(xq, lw["w"], xsf.view(ops.FP8_DTYPE), lw["sf"], lw["alpha"], self.dtype, out=out)
+
+    def _reduce_fp4(self, xq: torch.Tensor, xsf: torch.Tensor, lw, which: int) -> torch.Tensor:
+        """Row-parallel NVFP4 linear + sum over the ranks."""
+        if self.par is None:
+            return self._all_reduce(self._mm_fp4(xq, xsf, lw))
+        out = self.par.view(which, self.B, self.s.hidden)
+        self._mm_fp4(xq, xsf, lw, out=out)
+        if self.tp <= 4 and not self.par.multicast_ptr:
+            return self.par.all_reduce_out(which, torch.empty_like(out))
+        self.par.all_reduce_(which)  # two-shot, in place (through the switch when the fabric has multicast)
+        return out
 
     def _row_parallel(self, x: torch.Tensor, lw, which: int) -> torch.Tensor:
         """Row-parallel linear (quant + GEMM, either weight format) + sum over the ranks; the GEMM writes its
@@ -234,8 +256,35 @@ class DecodeRunner:
         # previous layer still sit un-reduced in peer buffer 1
         fuse_ar = fused and self.par is not None and (self.tp <= 4 or bool(self.par.multicast_ptr))
         pending = False
+        fused4 = self.wq == "nvfp4" and self.fused
         for lw, kv in zip(self.layers, self.kv_caches):
             kc, vc = kv.unbind(0)
+            if fused4:
+                # NVFP4, 10-11 launches per layer: norm+quant, GEMM, rope+cache, attention (+combine), quant, GEMM
+                # (+ all-reduce), norm+quant, GEMM, silu*mul+quant, GEMM (+ all-reduce)
+                for name in ("qkv", "o", "gate_up", "down"):
+                    self._fp4_consts(lw[name])
+                xq, xsf = self._fp4_bufs(B, s.hidden)
+                ops.rms_norm_nvfp4_quant(hidden, lw["ln1"], s.rms_eps, lw["qkv"]["ags"], residual=residual, result=xq,
+                                         result_block_scale=xsf)
+                qkv = self._mm_fp4(xq, xsf, lw["qkv"])
+                q, k, v = qkv.split([self.Hq * self.D, self.Hkv * self.D, self.Hkv * self.D], dim=-1)
+                ops.rotary_embedding_and_cache_write(self.positions, q, k, v, self.D, self.cos_sin, kc, vc,
+                                                     self.slot_mapping, self.kv_dtype, self.k_scale, self.v_scale)
+                ops.paged_attention_decode(attn_out, q.view(B, self.Hq, self.D), kc, vc, self.block_table,
+                                           self.seq_lens, self.scale, self.max_ctx, self.kv_dtype, self.k_scale,
+                                           self.v_scale, num_splits=self.num_splits, workspace=self.attn_ws)
+                oq, osf = self._fp4_bufs(B, self.Hq * self.D)
+                ops.scaled_fp4_quant_out(attn_out.view(B, -1), lw["o"]["ags"], True, oq, osf)
+                hidden = self._reduce_fp4(oq, osf, lw["o"], 0)
+                xq, xsf = self._fp4_bufs(B, s.hidden)
+                ops.rms_norm_nvfp4_quant(hidden, lw["ln2"], s.rms_eps, lw["gate_up"]["ags"], residual=residual,
+                                         result=xq, result_block_scale=xsf)
+                gu = self._mm_fp4(xq, xsf, lw["gate_up"])
+                aq, asf = self._fp4_bufs(B, self.inter)
+                ops.silu_and_mul_nvfp4_quant(aq, asf, gu, lw["down"]["ags"])
+                hidden = self._reduce_fp4(aq, asf, lw["down"], 1)
+                continue
             if fused:
                 # 10 launches per layer: norm+quant, GEMM, rope+cache, attention (+combine), quant, GEMM,
                 # norm+quant, GEMM, silu*mul+quant, GEMM

@@ -476,6 +476,60 @@ def scaled_fp4_quant_out(input: torch.Tensor, input_global_scale: torch.Tensor, 
     _lib.check(rc, "scaled_fp4_quant")
 
 
+def silu_and_mul_nvfp4_quant(result: torch.Tensor, result_block_scale: torch.Tensor, input: torch.Tensor,
+                             input_global_scale: torch.Tensor) -> None:
+    """torch.ops._C.silu_and_mul_nvfp4_quant (torch_bindings.cpp:251-253): input [m, 2d] = [gate | up];
+    result uint8 [m, d/2]; result_block_scale = the swizzled scale buffer for [m, d] (fully rewritten)."""
+    _require_cuda(input, input_global_scale, result, result_block_scale)
+    input = input.reshape(-1, input.shape[-1])
+    m, d2 = input.shape
+    if d2 % 32:
+        raise RuntimeError(f"The N dimension must be multiple of 16. (got 2d = {d2})")
+    d = d2 // 2
+    if input.dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError(f"Unsupported input data type for quantize_to_fp4: {input.dtype}")
+    if result.dtype != torch.uint8 or result.numel() != m * d // 2 or not result.is_contiguous():
+        raise RuntimeError("silu_and_mul_nvfp4_quant: result must be contiguous uint8 [m, d/2]")
+    need = round_up(m, 128) * round_up(d // 16, 4)
+    if result_block_scale.numel() * result_block_scale.element_size() < need or not result_block_scale.is_contiguous():
+        raise RuntimeError("silu_and_mul_nvfp4_quant: result_block_scale buffer too small or not contiguous")
+    if not input.is_contiguous():
+        input = input.contiguous()
+    rc = _lib.load().b200_silu_and_mul_nvfp4_quant(result.data_ptr(), result_block_scale.data_ptr(), input.data_ptr(),
+                                                   input_global_scale.data_ptr(), m, d, _dt(input), _stream(input))
+    _lib.check(rc, "silu_and_mul_nvfp4_quant")
+
+
+def rms_norm_nvfp4_quant(input: torch.Tensor, weight: torch.Tensor, epsilon: float, input_global_scale: torch.Tensor,
+                         residual: torch.Tensor | None = None, result: torch.Tensor | None = None,
+                         result_block_scale: torch.Tensor | None = None) -> tuple[torch.Tensor, torch.Tensor]:
+    """(residual += input in place;) NVFP4 quant of RMSNorm(.) * weight with swizzled scales - one kernel for
+    fused_add_rms_norm + scaled_fp4_quant (no reference counterpart; bit-identical to that composition of ours).
+    Returns (uint8 [m, h/2], float8_e4m3fn scales)."""
+    _require_cuda(input, weight, input_global_scale)
+    h = input.shape[-1]
+    x = input.view(-1, h) if input.is_contiguous() else input.reshape(-1, h)
+    m = x.shape[0]
+    if h % 16:
+        raise RuntimeError(f"last dim has to be multiple of 16, but got {h}.")
+    if x.dtype not in (torch.float16, torch.bfloat16) or weight.dtype != x.dtype:
+        raise RuntimeError("rms_norm_nvfp4_quant: input and weight must both be fp16 or bf16")
+    if x.stride(-1) != 1:
+        x = x.contiguous()
+    if residual is not None and (residual.dtype != x.dtype or residual.numel() != m * h or not residual.is_contiguous()):
+        raise RuntimeError("rms_norm_nvfp4_quant: residual must be contiguous, same dtype and shape as input")
+    if result is None:
+        result = torch.empty((m, h // 2), device=x.device, dtype=torch.uint8)
+    if result_block_scale is None:
+        result_block_scale = create_fp4_scale_tensor(m, h, x.device, True)
+    rc = _lib.load().b200_rms_norm_nvfp4_quant(
+        result.data_ptr(), result_block_scale.data_ptr(), x.data_ptr(), weight.data_ptr(),
+        residual.data_ptr() if residual is not None else None, input_global_scale.data_ptr(), m, h, x.stride(0),
+        float(epsilon), _dt(x), _stream(x))
+    _lib.check(rc, "rms_norm_nvfp4_quant")
+    return result, result_block_scale.view(torch.float8_e4m3fn)
+
+
 def cutlass_scaled_fp4_mm(
     a: torch.Tensor,
     b: torch.Tensor,

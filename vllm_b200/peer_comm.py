@@ -109,6 +109,12 @@ class PeerAllReduce:
         """Sum buffer `index` over the ranks, in place, on the current stream."""
         from .ops import _stream
 
+        if self.multicast_ptr:  # two-shot through the switch: multimem.ld_reduce of my slice + one multicast store
+            rc = _lib.load().b200_nvls_all_reduce(self.multicast_ptr, self._bufs, self._pads, self.rank, self.world,
+                                                  self.numel, self._dt, index * self.numel * 2, self._pad_bytes,
+                                                  _stream(self.storage))
+            _lib.check(rc, "nvls_all_reduce")
+            return
         rc = _lib.load().b200_peer_all_reduce(self._bufs, self._pads, self.rank, self.world, self.numel, self._dt,
                                               index * self.numel * 2, self._pad_bytes, _stream(self.storage))
         _lib.check(rc, "peer_all_reduce")

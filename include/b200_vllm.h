@@ -445,9 +445,13 @@ void b200_debug_attn_trace(unsigned long long* device_buffer);
 /* fp8-cache decode kernel selection (tests / tuning): 1 = tcgen05 kernel, 0 = register-level kernel,
  * -1 = default (register-level unless B200_ATTN_FP8_TCGEN05=1). */
 void b200_debug_attn_fp8_tcgen05(int mode);
-/* Force the decode-regime work partition (tests / tuning): 0 whole tiles per CTA pair, 3 cluster split-K over
- * distributed shared memory, -1 automatic. */
+/* Force the decode-regime (M <= 256) kernel / work partition (tests / tuning): 0 whole tiles per CTA pair, 3 cluster
+ * split-K over distributed shared memory, 4 the persistent 2-CTA kernel (UMMA M = 128 / 256 across the pair, no K
+ * split), -1 automatic. */
 void b200_debug_gemm_mode(int mode);
+/* Debug aid: when set, the 2-CTA FP8 kernel also writes the raw TMEM image of its LAST tile, fp32
+ * [2 CTAs][128 lanes][accumulator columns], there (how the UMMA M = 128 data-path layout was verified). */
+void b200_debug_gemm_dump(float* device_buffer);
 
 #ifdef __cplusplus
 }

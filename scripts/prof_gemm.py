@@ -11,9 +11,13 @@ ap.add_argument("--m", type=int, default=128); ap.add_argument("--n", type=int, 
 ap.add_argument("--k", type=int, default=4096); ap.add_argument("--reps", type=int, default=6)
 ap.add_argument("--nvfp4", action="store_true")
 ap.add_argument("--trace", action="store_true", help="print the decode kernel's per-phase %%globaltimer stamps")
+ap.add_argument("--mode", type=int, default=-1, help="b200_debug_gemm_mode (4 = 2-CTA kernel for M <= 256)")
 a = ap.parse_args()
 dev = "cuda:0"
 sets = 6
+if a.mode != -1:
+    from vllm_b200 import _lib as _l
+    _l.load().b200_debug_gemm_mode(a.mode)
 if a.nvfp4:
     gs = torch.tensor([1.0], device=dev)
     W = [ops.scaled_fp4_quant((torch.randn(a.n, a.k, device=dev) * 0.5).to(torch.bfloat16), gs) for _ in range(sets)]
@@ -32,6 +36,9 @@ if a.trace:
     from vllm_b200 import _lib
     names = ["entry", "setup", "ring_filled", "first_full", "last_commit", "acc_ready", "published", "gathered",
              "out_done", "epi_end", "exit"]
+    if a.mode == 4:  # the 2-CTA kernel's stamps
+        names = ["entry", "setup", "weights_issued", "first_full", "last_commit", "acc_ready", "pdl_wait_done",
+                 "kb_STAGES_full", "out_done", "-", "exit"]
     buf = torch.zeros(512, 16, dtype=torch.int64, device=dev)
     lib = _lib.load()
     for rep in range(3):

@@ -97,11 +97,12 @@ DECODE_MNK = [(1, 256, 128), (16, 4096, 4096), (40, 1008, 1024), (128, 6144, 409
               (200, 4096, 14336), (256, 640, 512)]
 
 
-@pytest.mark.parametrize("mode", [0, 3])
+@pytest.mark.parametrize("mode", [0, 3, 4])
 @pytest.mark.parametrize("mnk", DECODE_MNK)
 def test_fp8_gemm_decode_partitions(ops, mnk, mode):
-    """Both work partitions of the decode-regime kernel (whole tiles per CTA pair / cluster split-K over DSMEM)
-    against the oracle, odd tile counts and ragged N included;
+    """Both work partitions of the decode-regime kernel (whole tiles per CTA pair / cluster split-K over DSMEM) and
+    the persistent 2-CTA kernel with UMMA M = 128 / 256 across the pair (mode 4) against the oracle, odd tile counts
+    and ragged N included;
     each must also be run-to-run deterministic (fixed summation order, no atomics on data)."""
     from vllm_b200 import _lib
 

@@ -86,6 +86,7 @@ SIGNATURES: dict[str, tuple] = {
     "b200_debug_attn_trace": (None, [vp]),
     "b200_debug_attn_fp8_tcgen05": (None, [i32]),
     "b200_debug_gemm_mode": (None, [i32]),
+    "b200_debug_gemm_dump": (None, [vp]),
 }
 
 _lib: C.CDLL | None = None

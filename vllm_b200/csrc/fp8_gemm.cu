@@ -272,11 +272,13 @@ int run_fp8_decode(void* out, const void* a, const void* b, const float* a_scale
                    const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc, int a_scales_numel,
                    int b_scales_numel, void* workspace, size_t workspace_bytes, cudaStream_t stream);
 
+int gemm_debug_mode();  // fp8_gemm_decode.cu
+
 // large M: persistent 2-CTA kernel (gemm_persist.cu); returns 1 when it does not take the shape
 template <typename OutT>
 int run_fp8_gemm_2sm(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
                      const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc, int a_scales_numel,
-                     int b_scales_numel, cudaStream_t stream);
+                     int b_scales_numel, cudaStream_t stream, bool decode);
 
 template <typename OutT>
 static int run_fp8_gemm(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
@@ -294,6 +296,25 @@ static int run_fp8_gemm(void* out, const void* a, const void* b, const float* a_
   g.K = K;
   g.a_scales_numel = a_scales_numel;
   g.b_scales_numel = b_scales_numel;
+  // Decode regime, which kernel (same-box A/B on B200, profiles/r02_gemm_decode_2sm.md): the 2-CTA kernel with UMMA
+  // M = 128 / 256 across the pair (tokens on M, no K split, no fix-up) wins from 65 tokens up when its 128-wide
+  // tiles fit ONE wave of SM pairs and K <= 8192 (qkv 10.7 -> 9.6 us at M = 128, 14.1 -> 10.9 at M = 256; o 12.8 ->
+  // 10.0 at M = 256).  Otherwise the swap-AB kernel of fp8_gemm_decode.cu stays: long K with few tiles (down_proj)
+  // needs its cluster split-K to keep enough weight bytes in flight, gate_up's 224 tiles are a 3.03-wave tail
+  // here, and up to 64 tokens its token tile is 2-8 KB per k-block instead of 16 KB, so its ring is nearly all
+  // weights.
+  static const int decode_2sm = [] {
+    const char* e = getenv("B200_GEMM_DECODE_2SM");  // 0 = never, 1 = the policy above (default), 2 = always
+    return (e && *e) ? atoi(e) : 1;
+  }();
+  const int dbg = gemm_debug_mode();  // 4 forces the 2-CTA kernel, 0 / 3 force a partition of the decode kernel
+  const bool policy = decode_2sm == 2 ||
+                      (decode_2sm == 1 && M > 64 && K <= 8192 && (N + 127) / 128 <= sm_count() / 2);
+  if (M <= 256 && (dbg == 4 || (dbg == -1 && policy))) {
+    const int r2 = run_fp8_gemm_2sm<OutT>(out, a, b, a_scales, b_scales, bias, M, N, K, lda, ldb, ldc, a_scales_numel,
+                                          b_scales_numel, stream, true);
+    if (r2 <= 0) return r2;
+  }
   if (M <= 256)
     return run_fp8_decode<OutT>(out, a, b, a_scales, b_scales, bias, M, N, K, lda, ldb, ldc, a_scales_numel,
                                 b_scales_numel, workspace, workspace_bytes, stream);
@@ -303,7 +324,7 @@ static int run_fp8_gemm(void* out, const void* a, const void* b, const float* a_
   }();
   if (use_2sm) {
     const int r2 = run_fp8_gemm_2sm<OutT>(out, a, b, a_scales, b_scales, bias, M, N, K, lda, ldb, ldc, a_scales_numel,
-                                          b_scales_numel, stream);
+                                          b_scales_numel, stream, false);
     if (r2 <= 0) return r2;
   }
   CUtensorMap tx, ty;

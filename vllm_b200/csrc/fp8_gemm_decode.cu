@@ -527,6 +527,8 @@ static int launch_fp8_decode(const CUtensorMap& tw, const CUtensorMap& ta, const
 
 static unsigned long long* g_gemm_trace = nullptr;
 static int g_gemm_mode = -1;  // b200_debug_gemm_mode
+int gemm_debug_mode() { return g_gemm_mode; }
+unsigned long long* gemm_debug_trace() { return g_gemm_trace; }
 
 static int decode_bn(int M) { return M <= 16 ? 16 : (M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256))); }
 

@@ -535,7 +535,9 @@ static int ar_rms_norm_quant_impl(void* result, float* scales, const uint64_t* p
   B200_CHECK_ARG(reinterpret_cast<uintptr_t>(weight) % 16 == 0 && reinterpret_cast<uintptr_t>(residual) % 16 == 0 &&
                      reinterpret_cast<uintptr_t>(result) % 4 == 0,
                  B200_ERR_ALIGNMENT, "peer_all_reduce_rms_norm_quant: weight/residual must be 16-byte aligned");
-  int64_t grid = num_tokens < 64 ? num_tokens : 64;
+  // one row per CTA up to 128 CTAs (every row pays a peer-load / switch round trip: rows in flight, not bytes, set
+  // the duration), bounded by the signal pad and by one co-resident wave
+  int64_t grid = num_tokens < 128 ? num_tokens : 128;
   const int64_t max_grid = signal_pad_bytes / (kArSlotWords * 4);
   if (emu && grid > sm_count() / world_size) grid = sm_count() / world_size;  // one cooperative wave
   if (grid > max_grid) grid = max_grid;

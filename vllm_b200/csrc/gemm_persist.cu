@@ -27,17 +27,28 @@ namespace b200 {
 
 int get_kmajor_tmap(CUtensorMap* out, const void* base, int rows, int k_bytes, int64_t ld_bytes, int box_rows);
 
+unsigned long long* gemm_debug_trace();  // fp8_gemm_decode.cu (b200_debug_gemm_trace)
+
 constexpr int kP2Threads = 320;  // TMA warp, MMA warp, 8 epilogue warps (two per TMEM lane quarter)
 constexpr int kP2BK = 128;  // bytes of K per stage (one 128-byte swizzle span = 128 fp8)
 
-template <int BN> struct P2Cfg {
-  static constexpr int A_BYTES = 128 * kP2BK;         // this CTA's 128 token rows
+// UM = UMMA M across the pair: 256 (each CTA owns 128 token rows; TMEM lane = row, BN columns per accumulator) or
+// 128 (decode regime: each CTA owns 64 token rows; TMEM data-path "layout B": lanes 0-63 hold rows 0-63 x columns
+// [0, BN/2), lanes 64-127 hold the SAME rows x columns [BN/2, BN), so an accumulator is BN/2 TMEM columns wide).
+template <int UM, int BN> struct P2Cfg {
+  static constexpr int A_ROWS = UM / 2;               // this CTA's token rows
+  static constexpr int A_BYTES = A_ROWS * kP2BK;
   static constexpr int B_BYTES = (BN / 2) * kP2BK;    // this CTA's half of the weight tile
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > 8 ? 8 : (200 * 1024) / STAGE_BYTES;
-  static constexpr int TMEM_COLS = 2 * BN <= 32 ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
+  static constexpr int MAX_STAGES = UM == 128 ? 12 : 8;  // decode: latency-bound stream, keep more bytes in flight
+  static constexpr int STAGES = (200 * 1024) / STAGE_BYTES > MAX_STAGES ? MAX_STAGES : (200 * 1024) / STAGE_BYTES;
+  static constexpr int ACC_COLS = UM == 256 ? BN : BN / 2;
+  static constexpr int TMEM_COLS =
+      2 * ACC_COLS <= 32 ? 32 : (2 * ACC_COLS <= 64 ? 64 : (2 * ACC_COLS <= 128 ? 128 : (2 * ACC_COLS <= 256 ? 256 : 512)));
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 512 /*barriers*/;
-  static_assert(2 * BN <= 512, "two accumulators must fit the 512 TMEM columns");
+  static_assert(UM == 128 || UM == 256, "UMMA M across the pair");
+  static_assert(2 * ACC_COLS <= 512, "two accumulators must fit the 512 TMEM columns");
+  static_assert((2 * STAGES + 4) * 8 + 8 <= 512, "barrier area");
 };
 
 struct P2Args {
@@ -49,7 +60,13 @@ struct P2Args {
   int M, N, K;
   int a_scales_numel, b_scales_numel;
   int tiles_m, tiles_n, num_kb;
+  float* dump;  // debug only (b200_debug_gemm_dump), normally null
+  unsigned long long* trace;  // debug only (b200_debug_gemm_trace): [gridDim.x][16] %globaltimer stamps
 };
+// phase stamps for scripts/prof_gemm.py --trace (slot names there); one thread per CTA writes each slot
+__device__ __forceinline__ void p2_stamp(const P2Args& g, int slot) {
+  if (g.trace) g.trace[(size_t)blockIdx.x * 16 + slot] = globaltimer_ns();
+}
 
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // shared::cluster address of the same offset in CTA rank 0 of the pair
 
@@ -60,6 +77,12 @@ __device__ __forceinline__ uint32_t p2_cluster_ctarank() {
 }
 __device__ __forceinline__ void p2_cluster_sync() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// Final rendezvous of the pair before TMEM dealloc / exit.  It only keeps each CTA's shared memory and barriers
+// alive until the other is done with them (all such accesses were already observed complete through tmem_full);
+// RELAXED, because the .release form first drains the epilogue warps' output stores (~0.5 us at the kernel's tail).
+__device__ __forceinline__ void p2_cluster_sync_exit() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory");
 }
 // TMA load whose completion bytes are counted on the LEADER CTA's mbarrier (executed by both CTAs of the pair)
 __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const void* tmap, uint64_t* bar, int c0, int c1,
@@ -123,11 +146,79 @@ __device__ __forceinline__ void st_global_256(void* dst, const uint32_t (&w)[8])
                : "memory");
 }
 
-template <int BN, typename OutT>
+// Epilogue of the 2-CTA kernels (both CTAs, warps 2-9): warp w owns TMEM lanes 32*(w%4).. and half of that lane
+// quarter's columns; tcgen05.ld -> scales (+ bias) -> 16-bit -> one 256-bit store per 16 columns, then the
+// accumulator is handed back to the leader's MMA warp.
+template <int UM, int BN, int ACC_COLS, typename OutT>
+__device__ __forceinline__ void p2_epilogue(const P2Args& g, uint32_t tmem_base, uint64_t* tmem_full_bar,
+                                            uint64_t* tmem_empty_bar, int warp, int lane, int rank, int pair,
+                                            int num_pairs) {
+  const int num_tiles = g.tiles_m * g.tiles_n;
+  const int q = warp & 3;
+  OutT* outp = reinterpret_cast<OutT*>(g.out);
+  const OutT* bias = reinterpret_cast<const OutT*>(g.bias);
+  const bool vec_ok = ((g.ldc * (int64_t)sizeof(OutT)) % 32 == 0) && (reinterpret_cast<uintptr_t>(g.out) % 32 == 0);
+  const float bs0 = g.b_scales[0];
+  int it = 0;
+  for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+    const int tm = t % g.tiles_m, tn = t / g.tiles_m;
+    const int acc = it & 1;
+    // UM = 256: lane quarter q = rows 32q.., all BN columns.  UM = 128: quarters 0,1 = rows 0..63 x columns
+    // [0, BN/2), quarters 2,3 = the same rows x columns [BN/2, BN) (TMEM columns [0, BN/2) in both cases).
+    const int m = UM == 256 ? tm * 256 + rank * 128 + q * 32 + lane : tm * 128 + rank * 64 + (q & 1) * 32 + lane;
+    const int n0 = tn * BN + (UM == 256 ? 0 : (q >> 1) * (BN / 2));
+    const float as = m < g.M ? g.a_scales[g.a_scales_numel > 1 ? m : 0] : 0.f;
+    mbar_wait(&tmem_full_bar[acc], ((uint32_t)it >> 1) & 1);
+    umma::fence_after_sync();
+    if (warp == 2 && lane == 0 && t + num_pairs >= num_tiles) p2_stamp(g, 5);
+    const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + acc * ACC_COLS;
+    uint32_t rn[16];
+    // the two warps of a lane quarter split that quarter's columns
+    const int c_lo = ((warp - 2) >> 2) * (ACC_COLS / 2), c_hi = c_lo + ACC_COLS / 2;
+    umma::ld_32x32b_x16(tacc + c_lo, rn);
+#pragma unroll 1
+    for (int c = c_lo; c < c_hi; c += 16) {
+      umma::ld_wait_dep(rn);
+      float v[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(rn[j]);
+      if (c + 16 < c_hi) umma::ld_32x32b_x16(tacc + c + 16, rn);  // next chunk in flight while this one is stored
+      if (g.dump) {  // debug: raw TMEM image [cta][lane][column] (b200_debug_gemm_dump)
+        float* d = g.dump + ((int64_t)(rank * 128 + q * 32 + lane)) * ACC_COLS + c;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) d[j] = v[j];
+      }
+      const int n = n0 + c;
+      if (m < g.M && n < g.N) {  // N % 16 == 0: a chunk is entirely inside or outside
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const float bs = g.b_scales_numel > 1 ? g.b_scales[n + j] : bs0;
+          v[j] = v[j] * as * bs + (bias ? to_float(bias[n + j]) : 0.f);
+        }
+        OutT* dst = outp + (int64_t)m * g.ldc + n;
+        if (vec_ok) {
+          uint32_t w[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) w[i] = p2_pack2<OutT>(v[2 * i], v[2 * i + 1]);
+          st_global_256(dst, w);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) dst[j] = from_float<OutT>(v[j]);
+        }
+      }
+    }
+    umma::fence_before_sync();
+    __syncwarp();
+    if (lane == 0) mbar_arrive_leader(&tmem_empty_bar[acc]);
+    if (warp == 2 && lane == 0 && t + num_pairs >= num_tiles) p2_stamp(g, 8);
+  }
+}
+
+template <int UM, int BN, typename OutT>
 __global__ void __launch_bounds__(kP2Threads, 1)
     fp8_gemm_2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                         const P2Args g) {
-  using Cfg = P2Cfg<BN>;
+  using Cfg = P2Cfg<UM, BN>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
@@ -143,6 +234,7 @@ __global__ void __launch_bounds__(kP2Threads, 1)
   const int num_tiles = g.tiles_m * g.tiles_n;
 
   if (threadIdx.x == 0) {
+    p2_stamp(g, 0);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(&full_bar[s], 1);   // the leader's arrive.expect_tx covers BOTH CTAs' bytes (see the producer)
       mbar_init(&empty_bar[s], 1);  // multicast tcgen05.commit
@@ -161,19 +253,44 @@ __global__ void __launch_bounds__(kP2Threads, 1)
   umma::fence_after_sync();
   const uint32_t tmem_base = *tmem_slot;
   pdl_trigger();
-  pdl_wait();
+  if (warp != 0) pdl_wait();  // (the producer waits after its weight prologue)
 
   if (warp == 0) {
-    // ===== TMA producer (both CTAs): my 128 rows of A, my BN/2 rows of B =====
+    // ===== TMA producer (both CTAs): my UM/2 rows of A, my BN/2 rows of B =====
     if (umma::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      // The WEIGHTS do not depend on the preceding kernel: fill the ring with the first tile's weight halves while
+      // the predecessor drains, only then wait for the activations (programmatic dependent launch).
+      int pre = 0;
+      p2_stamp(g, 1);
+      if (pair < num_tiles) {
+        pre = g.num_kb < STAGES ? g.num_kb : STAGES;
+        const int b_row0 = (pair / g.tiles_m) * BN + rank * (BN / 2);
+        for (int i = 0; i < pre; ++i) {
+          if (rank == 0) mbar_arrive_expect_tx(&full_bar[i], 2 * Cfg::STAGE_BYTES);
+          tma_load_2d_2sm(smem + i * Cfg::STAGE_BYTES + Cfg::A_BYTES, &tmap_b, &full_bar[i], i * kP2BK, b_row0,
+                          UM == 128 ? kEvictFirst : kEvictNormal);
+        }
+      }
+      p2_stamp(g, 2);
+      pdl_wait();
+      p2_stamp(g, 6);
       for (int t = pair; t < num_tiles; t += num_pairs) {
         const int tm = t % g.tiles_m, tn = t / g.tiles_m;
-        const int a_row = tm * 256 + rank * 128, b_row = tn * BN + rank * (BN / 2);
+        const int a_row = tm * UM + rank * Cfg::A_ROWS, b_row = tn * BN + rank * (BN / 2);
         for (int kb = 0; kb < g.num_kb; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+          if (pre > 0) {  // this slot's weights are already on their way
+            --pre;
+            tma_load_2d_2sm(sa, &tmap_a, &full_bar[stage], kb * kP2BK, a_row, UM == 128 ? kEvictLast : kEvictNormal);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1;
+            }
+            continue;
+          }
+          mbar_wait(&empty_bar[stage], phase ^ 1);
           // Byte counting alone synchronises the pair: the leader expects both CTAs' bytes; the peer only issues
           // its loads (complete_tx on the leader's barrier).  The peer cannot run ahead into the next phase of
           // this slot because its own empty[] barrier is signalled by the MMAs that consumed the current one.
@@ -181,8 +298,9 @@ __global__ void __launch_bounds__(kP2Threads, 1)
           // one thread that issues the peer's loads: 0.8 us per k-block, 35 % tensor-pipe utilisation -
           // profiles/r02_gemm2sm_ncu.md.)
           if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * Cfg::STAGE_BYTES);
-          tma_load_2d_2sm(sa, &tmap_a, &full_bar[stage], kb * kP2BK, a_row, kEvictNormal);
-          tma_load_2d_2sm(sa + Cfg::A_BYTES, &tmap_b, &full_bar[stage], kb * kP2BK, b_row, kEvictNormal);
+          tma_load_2d_2sm(sa, &tmap_a, &full_bar[stage], kb * kP2BK, a_row, UM == 128 ? kEvictLast : kEvictNormal);
+          tma_load_2d_2sm(sa + Cfg::A_BYTES, &tmap_b, &full_bar[stage], kb * kP2BK, b_row,
+                          UM == 128 ? kEvictFirst : kEvictNormal);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
@@ -193,7 +311,7 @@ __global__ void __launch_bounds__(kP2Threads, 1)
   } else if (warp == 1) {
     // ===== MMA issuer (leader CTA only) =====
     if (rank == 0 && umma::elect_one()) {
-      constexpr uint32_t idesc = umma::make_idesc_f8(256, BN);
+      constexpr uint32_t idesc = umma::make_idesc_f8(UM, BN);
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -201,10 +319,12 @@ __global__ void __launch_bounds__(kP2Threads, 1)
         const int acc = it & 1;
         mbar_wait(&tmem_empty_bar[acc], (((uint32_t)it >> 1) & 1) ^ 1);  // both CTAs' epilogues drained this buffer
         umma::fence_after_sync();
-        const uint32_t tacc = tmem_base + acc * BN;
+        const uint32_t tacc = tmem_base + acc * Cfg::ACC_COLS;
         for (int kb = 0; kb < g.num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           umma::fence_after_sync();
+          if (it == 0 && kb == 0) p2_stamp(g, 3);
+          if (it == 0 && kb == STAGES) p2_stamp(g, 7);
           const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
           const uint64_t da = umma::make_desc_k_sw128(sa);
           const uint64_t db = umma::make_desc_k_sw128(sa + Cfg::A_BYTES);
@@ -220,67 +340,190 @@ __global__ void __launch_bounds__(kP2Threads, 1)
         }
         commit_2sm(&tmem_full_bar[acc]);  // accumulator complete: both CTAs' epilogues may drain their halves
       }
+      p2_stamp(g, 4);
     }
   } else {
-    // ===== epilogue (both CTAs): warp w owns TMEM lanes 32*(w%4).. = token rows of this CTA's half =====
-    const int q = warp & 3;
-    OutT* outp = reinterpret_cast<OutT*>(g.out);
-    const OutT* bias = reinterpret_cast<const OutT*>(g.bias);
-    const bool vec_ok = ((g.ldc * (int64_t)sizeof(OutT)) % 32 == 0) && (reinterpret_cast<uintptr_t>(g.out) % 32 == 0);
-    const float bs0 = g.b_scales[0];
-    int it = 0;
-    for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
-      const int tm = t % g.tiles_m, tn = t / g.tiles_m;
-      const int acc = it & 1;
-      const int m = tm * 256 + rank * 128 + q * 32 + lane;
-      const int n0 = tn * BN;
-      const float as = m < g.M ? g.a_scales[g.a_scales_numel > 1 ? m : 0] : 0.f;
-      mbar_wait(&tmem_full_bar[acc], ((uint32_t)it >> 1) & 1);
-      umma::fence_after_sync();
-      const uint32_t tacc = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
-      uint32_t rn[16];
-      const int c_lo = ((warp - 2) >> 2) * (BN / 2), c_hi = c_lo + BN / 2;  // the two warps of a lane quarter split the columns
-      umma::ld_32x32b_x16(tacc + c_lo, rn);
-#pragma unroll 1
-      for (int c = c_lo; c < c_hi; c += 16) {
-        umma::ld_wait_dep(rn);
-        float v[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(rn[j]);
-        if (c + 16 < c_hi) umma::ld_32x32b_x16(tacc + c + 16, rn);  // next chunk in flight while this one is stored
-        const int n = n0 + c;
-        if (m < g.M && n < g.N) {  // N % 16 == 0: a chunk is entirely inside or outside
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float bs = g.b_scales_numel > 1 ? g.b_scales[n + j] : bs0;
-            v[j] = v[j] * as * bs + (bias ? to_float(bias[n + j]) : 0.f);
-          }
-          OutT* dst = outp + (int64_t)m * g.ldc + n;
-          if (vec_ok) {
-            uint32_t w[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) w[i] = p2_pack2<OutT>(v[2 * i], v[2 * i + 1]);
-            st_global_256(dst, w);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) dst[j] = from_float<OutT>(v[j]);
+    p2_epilogue<UM, BN, Cfg::ACC_COLS, OutT>(g, tmem_base, tmem_full_bar, tmem_empty_bar, warp, lane, rank, pair, num_pairs);
+  }
+  umma::fence_before_sync();
+  p2_cluster_sync_exit();  // the leader's MMAs read the peer's shared memory; multicast arrives target both CTAs
+  if (warp == 1) tmem_dealloc_2sm<Cfg::TMEM_COLS>(tmem_base);
+  if (threadIdx.x == 0) p2_stamp(g, 10);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Decode regime (M <= 256) on the same pair structure, with the two operands in SEPARATE rings.
+// The weights stream from HBM once and nothing else does: what bounds the kernel is how many weight bytes each SM
+// keeps in flight (HBM latency ~2 us x 6.5 TB/s = ~13 MB over the chip).  With one combined ring half (BN = 128) or
+// two thirds (BN = 64) of every stage is the token tile, which comes from L2 and needs no depth.  Here the token
+// ring has 4 slots and the weight ring takes the rest of shared memory (BN = 128: 21 x 8 KB, BN = 64: 32 x 4 KB
+// per CTA at UM = 128), its producer never waits for the preceding kernel (the weights do not depend on it:
+// programmatic dependent launch lets the ring fill while the predecessor drains), and no K split and no fix-up
+// are needed because a pair streams a whole K row block.  Warps: 0 weight producer, 1 TMEM alloc + MMA (leader),
+// 2-9 epilogue, 10 token producer.
+constexpr int kD2Threads = 352;
+
+template <int UM, int BN> struct D2Cfg {
+  static constexpr int A_ROWS = UM / 2;
+  static constexpr int A_BYTES = A_ROWS * kP2BK;
+  static constexpr int B_BYTES = (BN / 2) * kP2BK;
+  static constexpr int A_STAGES = 4;
+  static constexpr int B_FIT = (200 * 1024 - A_STAGES * A_BYTES) / B_BYTES;
+  static constexpr int B_STAGES = B_FIT > 32 ? 32 : B_FIT;
+  static constexpr int ACC_COLS = UM == 256 ? BN : BN / 2;
+  static constexpr int TMEM_COLS =
+      2 * ACC_COLS <= 32 ? 32 : (2 * ACC_COLS <= 64 ? 64 : (2 * ACC_COLS <= 128 ? 128 : (2 * ACC_COLS <= 256 ? 256 : 512)));
+  static constexpr int BAR_BYTES = (2 * A_STAGES + 2 * B_STAGES + 4) * 8 + 16;
+  static constexpr int SMEM_BYTES = A_STAGES * A_BYTES + B_STAGES * B_BYTES + 1024 /*align*/ + 1024 /*barriers*/;
+  static_assert(BAR_BYTES <= 1024, "barrier area");
+};
+
+template <int UM, int BN, typename OutT>
+__global__ void __launch_bounds__(kD2Threads, 1)
+    fp8_gemm_2sm_decode_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                               const P2Args g) {
+  using Cfg = D2Cfg<UM, BN>;
+  constexpr int AS = Cfg::A_STAGES, BS = Cfg::B_STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align_smem_1024(smem_raw);
+  uint8_t* ring_a = smem;
+  uint8_t* ring_b = smem + AS * Cfg::A_BYTES;
+  uint64_t* full_a = reinterpret_cast<uint64_t*>(ring_b + BS * Cfg::B_BYTES);
+  uint64_t* empty_a = full_a + AS;
+  uint64_t* full_b = empty_a + AS;
+  uint64_t* empty_b = full_b + BS;
+  uint64_t* tmem_full_bar = empty_b + BS;        // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;  // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = (int)p2_cluster_ctarank();
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  const int num_tiles = g.tiles_m * g.tiles_n;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < AS; ++s) {
+      mbar_init(&full_a[s], 1);  // the leader's arrive.expect_tx covers both CTAs' bytes
+      mbar_init(&empty_a[s], 1);
+    }
+    for (int s = 0; s < BS; ++s) {
+      mbar_init(&full_b[s], 1);
+      mbar_init(&empty_b[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full_bar[b], 1);
+      mbar_init(&tmem_empty_bar[b], 16);
+    }
+    fence_barrier_init();
+    prefetch_tensormap(&tmap_a);
+    prefetch_tensormap(&tmap_b);
+  }
+  if (warp == 1) tmem_alloc_2sm<Cfg::TMEM_COLS>(tmem_slot);
+  umma::fence_before_sync();
+  p2_cluster_sync();
+  umma::fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_trigger();
+
+  if (warp == 0) {
+    // ===== weight producer (both CTAs): my BN/2 rows of every k-block of every tile of this pair; never waits
+    // for the preceding kernel =====
+    if (umma::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = pair; t < num_tiles; t += num_pairs) {
+        const int b_row = (t / g.tiles_m) * BN + rank * (BN / 2);
+        for (int kb = 0; kb < g.num_kb; ++kb) {
+          mbar_wait(&empty_b[stage], phase ^ 1);
+          if (rank == 0) mbar_arrive_expect_tx(&full_b[stage], 2 * Cfg::B_BYTES);
+          tma_load_2d_2sm(ring_b + stage * Cfg::B_BYTES, &tmap_b, &full_b[stage], kb * kP2BK, b_row, kEvictFirst);
+          if (++stage == BS) {
+            stage = 0;
+            phase ^= 1;
           }
         }
       }
-      umma::fence_before_sync();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_leader(&tmem_empty_bar[acc]);
     }
+  } else if (warp == 10) {
+    // ===== token producer (both CTAs): my UM/2 rows, from L2 after the first pair has pulled them in =====
+    if (umma::elect_one()) {
+      pdl_wait();  // the activations are the preceding kernel's output
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = pair; t < num_tiles; t += num_pairs) {
+        const int a_row = (t % g.tiles_m) * UM + rank * Cfg::A_ROWS;
+        for (int kb = 0; kb < g.num_kb; ++kb) {
+          mbar_wait(&empty_a[stage], phase ^ 1);
+          if (rank == 0) mbar_arrive_expect_tx(&full_a[stage], 2 * Cfg::A_BYTES);
+          tma_load_2d_2sm(ring_a + stage * Cfg::A_BYTES, &tmap_a, &full_a[stage], kb * kP2BK, a_row, kEvictLast);
+          if (++stage == AS) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (leader CTA only) =====
+    if (rank == 0 && umma::elect_one()) {
+      constexpr uint32_t idesc = umma::make_idesc_f8(UM, BN);
+      int sa = 0, sb = 0;
+      uint32_t pa = 0, pb = 0;
+      int it = 0;
+      for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+        const int acc = it & 1;
+        mbar_wait(&tmem_empty_bar[acc], (((uint32_t)it >> 1) & 1) ^ 1);
+        umma::fence_after_sync();
+        const uint32_t tacc = tmem_base + acc * Cfg::ACC_COLS;
+        for (int kb = 0; kb < g.num_kb; ++kb) {
+          mbar_wait(&full_b[sb], pb);
+          mbar_wait(&full_a[sa], pa);
+          umma::fence_after_sync();
+          const uint64_t da = umma::make_desc_k_sw128(smem_u32(ring_a + sa * Cfg::A_BYTES));
+          const uint64_t db = umma::make_desc_k_sw128(smem_u32(ring_b + sb * Cfg::B_BYTES));
+#pragma unroll
+          for (int kk = 0; kk < kP2BK / 32; ++kk)
+            mma_f8f6f4_2sm(tacc, umma::desc_advance(da, kk * 32), umma::desc_advance(db, kk * 32), idesc,
+                           (kb | kk) != 0);
+          commit_2sm(&empty_a[sa]);  // each frees its slot in both CTAs
+          commit_2sm(&empty_b[sb]);
+          if (++sa == AS) {
+            sa = 0;
+            pa ^= 1;
+          }
+          if (++sb == BS) {
+            sb = 0;
+            pb ^= 1;
+          }
+        }
+        commit_2sm(&tmem_full_bar[acc]);
+      }
+    }
+  } else {
+    pdl_wait();  // scales, bias and the output buffer belong to the stream order from here
+    p2_epilogue<UM, BN, Cfg::ACC_COLS, OutT>(g, tmem_base, tmem_full_bar, tmem_empty_bar, warp, lane, rank, pair,
+                                            num_pairs);
   }
   umma::fence_before_sync();
-  p2_cluster_sync();  // the leader's MMAs read the peer's shared memory; multicast arrives target both CTAs
+  p2_cluster_sync();
   if (warp == 1) tmem_dealloc_2sm<Cfg::TMEM_COLS>(tmem_base);
 }
 
-template <int BN, typename OutT>
+template <int UM, int BN, typename OutT>
+static int launch_d2(const CUtensorMap& ta, const CUtensorMap& tb, const P2Args& g, int num_pairs, cudaStream_t stream) {
+  using Cfg = D2Cfg<UM, BN>;
+  auto kern = fp8_gemm_2sm_decode_kernel<UM, BN, OutT>;
+  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES)) return rc;
+  launch_kernel(kern, dim3(2 * num_pairs), dim3(kD2Threads), Cfg::SMEM_BYTES, stream, 2, ta, tb, g);
+  B200_CHECK_LAUNCH();
+  count_launch();
+  return 0;
+}
+
+template <int UM, int BN, typename OutT>
 static int launch_p2(const CUtensorMap& ta, const CUtensorMap& tb, const P2Args& g, int num_pairs, cudaStream_t stream) {
-  using Cfg = P2Cfg<BN>;
-  auto kern = fp8_gemm_2sm_kernel<BN, OutT>;
+  using Cfg = P2Cfg<UM, BN>;
+  auto kern = fp8_gemm_2sm_kernel<UM, BN, OutT>;
   if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES)) return rc;
   launch_kernel(kern, dim3(2 * num_pairs), dim3(kP2Threads), Cfg::SMEM_BYTES, stream, 2, ta, tb, g);
   B200_CHECK_LAUNCH();
@@ -288,26 +531,32 @@ static int launch_p2(const CUtensorMap& ta, const CUtensorMap& tb, const P2Args&
   return 0;
 }
 
-template <int BN, typename OutT>
+static float* g_p2_dump = nullptr;
+
+template <int UM, int BN, typename OutT, bool kDecode = false>
 static int run_p2(P2Args g, const void* a, const void* b, int64_t lda, int64_t ldb, cudaStream_t stream) {
+  g.tiles_m = (g.M + UM - 1) / UM;
   g.tiles_n = (g.N + BN - 1) / BN;
+  g.dump = g_p2_dump;
+  g.trace = gemm_debug_trace();
   CUtensorMap ta, tb;
   int rc;
-  if ((rc = get_kmajor_tmap(&ta, a, g.M, g.K, lda, 128))) return rc;
+  if ((rc = get_kmajor_tmap(&ta, a, g.M, g.K, lda, UM / 2))) return rc;
   if ((rc = get_kmajor_tmap(&tb, b, g.N, g.K, ldb, BN / 2))) return rc;
   const int tiles = g.tiles_m * g.tiles_n;
   int pairs = sm_count() / 2;
   if (pairs > tiles) pairs = tiles;
-  return launch_p2<BN, OutT>(ta, tb, g, pairs, stream);
+  if constexpr (kDecode) return launch_d2<UM, BN, OutT>(ta, tb, g, pairs, stream);
+  else return launch_p2<UM, BN, OutT>(ta, tb, g, pairs, stream);
 }
 
-// Returns 1 when the shape is not handled here (the caller falls back to the one-tile-per-CTA kernel), 0 on
-// success, a negative B200_ERR_* otherwise.
+// Returns 1 when the shape is not handled here (the caller falls back), 0 on success, a negative B200_ERR_*
+// otherwise.  M <= 256 (decode regime) is only taken when `decode` is set.
 template <typename OutT>
 int run_fp8_gemm_2sm(void* out, const void* a, const void* b, const float* a_scales, const float* b_scales,
                      const void* bias, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc, int a_scales_numel,
-                     int b_scales_numel, cudaStream_t stream) {
-  if (M <= 256 || N < 64) return 1;
+                     int b_scales_numel, cudaStream_t stream, bool decode) {
+  if ((M <= 256 && !decode) || N < 64) return 1;
   P2Args g;
   g.out = out;
   g.a_scales = a_scales;
@@ -319,28 +568,61 @@ int run_fp8_gemm_2sm(void* out, const void* a, const void* b, const float* a_sca
   g.K = K;
   g.a_scales_numel = a_scales_numel;
   g.b_scales_numel = b_scales_numel;
-  g.tiles_m = (M + 255) / 256;
+  g.tiles_m = 0;
   g.tiles_n = 0;
   g.num_kb = (K + kP2BK - 1) / kP2BK;
+  g.dump = nullptr;
+  g.trace = nullptr;
+  const long pairs = sm_count() / 2;
+  static const int force_bn = [] {
+    const char* e = getenv("B200_GEMM_2SM_BN");  // tuning aid: 64 (decode only) / 128 / 256
+    return (e && *e) ? atoi(e) : 0;
+  }();
+  if (M <= 256) {
+    // Decode regime: the weights stream once, every pair of SMs should be streaming.  One M tile (UMMA M = 128
+    // across the pair up to 128 tokens, else 256); the narrower weight tile when the wide one leaves SMs idle
+    // (o_proj / down_proj: N = 4096 -> 32 wide tiles for 74 pairs) or saves rounds of the persistent loop.
+    const long t128 = (N + 127) / 128, t64 = (N + 63) / 64;
+    const double cost128 = (double)((t128 + pairs - 1) / pairs), cost64 = 0.75 * (double)((t64 + pairs - 1) / pairs);
+    (void)cost64;
+    (void)cost128;
+    // 64-wide tiles only when the wide ones would occupy under a quarter of the pairs (measured: o_proj N = 4096
+    // 9.07 us with 32 wide tiles against 9.25-9.9 with 64 narrow ones - the narrow stage is 2/3 token bytes)
+    const bool narrow = force_bn ? force_bn == 64 : t128 * 4 <= pairs;
+    static const bool split_rings = [] {
+      const char* e = getenv("B200_GEMM_DECODE_RINGS");  // 1 = the split-ring kernel (measured slower, see above)
+      return e && *e && atoi(e) != 0;
+    }();
+    if (!split_rings) {
+      if (M <= 128) return narrow ? run_p2<128, 64, OutT>(g, a, b, lda, ldb, stream) : run_p2<128, 128, OutT>(g, a, b, lda, ldb, stream);
+      return narrow ? run_p2<256, 64, OutT>(g, a, b, lda, ldb, stream) : run_p2<256, 128, OutT>(g, a, b, lda, ldb, stream);
+    }
+    if (M <= 128)
+      return narrow ? run_p2<128, 64, OutT, true>(g, a, b, lda, ldb, stream)
+                    : run_p2<128, 128, OutT, true>(g, a, b, lda, ldb, stream);
+    return narrow ? run_p2<256, 64, OutT, true>(g, a, b, lda, ldb, stream)
+                  : run_p2<256, 128, OutT, true>(g, a, b, lda, ldb, stream);
+  }
   // Tile width.  256 x 256 is the balanced tile (a k-block's 32 KB per SM arrive in about the time its four
   // 256x256x32 MMAs take); 256 x 128 halves the MMA work per k-block but still needs 24 KB, so it costs ~0.7 of a
   // wide tile.  It wins when it does not add rounds of the persistent loop (few tiles: M = 512 o/down).
-  const long pairs = sm_count() / 2;
-  const long t256 = (long)g.tiles_m * ((N + 255) / 256), t128 = (long)g.tiles_m * ((N + 127) / 128);
+  const long tm = (M + 255) / 256;
+  const long t256 = tm * ((N + 255) / 256), t128 = tm * ((N + 127) / 128);
   const double cost256 = (double)((t256 + pairs - 1) / pairs), cost128 = 0.7 * (double)((t128 + pairs - 1) / pairs);
-  static const int force_bn = [] {
-    const char* e = getenv("B200_GEMM_2SM_BN");  // tuning aid: 128 / 256
-    return (e && *e) ? atoi(e) : 0;
-  }();
   const bool narrow = force_bn ? force_bn == 128 : (cost128 < cost256 || N < 256);
-  if (narrow) return run_p2<128, OutT>(g, a, b, lda, ldb, stream);
-  return run_p2<256, OutT>(g, a, b, lda, ldb, stream);
+  if (narrow) return run_p2<256, 128, OutT>(g, a, b, lda, ldb, stream);
+  return run_p2<256, 256, OutT>(g, a, b, lda, ldb, stream);
 }
 
 template int run_fp8_gemm_2sm<__nv_bfloat16>(void*, const void*, const void*, const float*, const float*, const void*,
-                                             int, int, int, int64_t, int64_t, int64_t, int, int, cudaStream_t);
+                                             int, int, int, int64_t, int64_t, int64_t, int, int, cudaStream_t, bool);
 template int run_fp8_gemm_2sm<__half>(void*, const void*, const void*, const float*, const float*, const void*, int, int,
-                                      int, int64_t, int64_t, int64_t, int, int, cudaStream_t);
+                                      int, int64_t, int64_t, int64_t, int, int, cudaStream_t, bool);
+}  // namespace b200
+
+extern "C" void b200_debug_gemm_dump(float* device_buffer) { b200::g_p2_dump = device_buffer; }
+
+namespace b200 {
 
 
 // ======================================================================================================
@@ -596,8 +878,8 @@ static int run_p4(P4Args g, const void* a, const void* b, const void* sfa, const
 // Returns 1 when the shape is not handled here (the caller uses nvfp4_gemm.cu), 0 on success, < 0 on error.
 template <typename OutT>
 int run_nvfp4_gemm_2sm(void* out, const void* a, const void* b, const void* sfa, const void* sfb, const float* alpha,
-                       int M, int N, int K, int64_t ldc, cudaStream_t stream) {
-  if (M <= 256 || N < 128 || K % 32) return 1;
+                       int M, int N, int K, int64_t ldc, cudaStream_t stream, int min_m) {
+  if (M <= min_m || N < 128 || K % 32) return 1;
   P4Args g;
   g.out = out;
   g.alpha = alpha;
@@ -624,8 +906,8 @@ int run_nvfp4_gemm_2sm(void* out, const void* a, const void* b, const void* sfa,
 }
 
 template int run_nvfp4_gemm_2sm<__nv_bfloat16>(void*, const void*, const void*, const void*, const void*, const float*,
-                                               int, int, int, int64_t, cudaStream_t);
+                                               int, int, int, int64_t, cudaStream_t, int);
 template int run_nvfp4_gemm_2sm<__half>(void*, const void*, const void*, const void*, const void*, const float*, int, int,
-                                        int, int64_t, cudaStream_t);
+                                        int, int64_t, cudaStream_t, int);
 
 }  // namespace b200

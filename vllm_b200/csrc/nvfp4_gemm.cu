@@ -368,7 +368,7 @@ static int launch_f4(const CUtensorMap& tx, const CUtensorMap& ty, const F4Args&
 // large M: persistent 2-CTA kernel (gemm_persist.cu); returns 1 when it does not take the shape
 template <typename OutT>
 int run_nvfp4_gemm_2sm(void* out, const void* a, const void* b, const void* sfa, const void* sfb, const float* alpha,
-                       int M, int N, int K, int64_t ldc, cudaStream_t stream);
+                       int M, int N, int K, int64_t ldc, cudaStream_t stream, int min_m);
 
 template <typename OutT>
 static int run_f4(void* out, const void* a, const void* b, const void* sfa, const void* sfb, const float* alpha,
@@ -381,6 +381,14 @@ static int run_f4(void* out, const void* a, const void* b, const void* sfa, cons
   g.N = N;
   g.K = K;
   g.num_k_atoms = (K + 63) / 64;
+  static const int decode_2sm = [] {
+    const char* e = getenv("B200_F4_DECODE_2SM");  // tuning aid: M threshold above which M <= 256 also runs on the
+    return (e && *e) ? atoi(e) : 0;                // persistent 2-CTA kernel (0 = never)
+  }();
+  if (decode_2sm > 0 && M > decode_2sm && M <= 256) {
+    const int r2 = run_nvfp4_gemm_2sm<OutT>(out, a, b, sfa, sfb, alpha, M, N, K, ldc, stream, decode_2sm);
+    if (r2 <= 0) return r2;
+  }
   CUtensorMap tx, ty;
   int rc;
   const int kb = K / 2;
@@ -434,7 +442,7 @@ static int run_f4(void* out, const void* a, const void* b, const void* sfa, cons
     return !(e && *e && atoi(e) == 0);
   }();
   if (use_2sm && M > 256) {
-    const int r2 = run_nvfp4_gemm_2sm<OutT>(out, a, b, sfa, sfb, alpha, M, N, K, ldc, stream);
+    const int r2 = run_nvfp4_gemm_2sm<OutT>(out, a, b, sfa, sfb, alpha, M, N, K, ldc, stream, 256);
     if (r2 <= 0) return r2;
   }
   g.sfx = reinterpret_cast<const uint8_t*>(sfa);

@@ -28,14 +28,16 @@ class PeerAllReduce:
         if numel % (8 * self.world):
             raise RuntimeError(f"PeerAllReduce: numel {numel} must be a multiple of 8 * world_size")
         self.dtype, self.numel, self.num_buffers = dtype, numel, num_buffers
-        self.storage = symm_mem.empty(num_buffers * numel, dtype=dtype, device=device)
+        # The barrier flags live in the SAME symmetric allocation, behind the buffers: 128 bytes per CTA, room for
+        # 256 CTAs (torch's own signal pad only has room for 72, which capped the fused kernel at 64 rows in flight).
+        self._pad_bytes = 256 * 128
+        self.storage = symm_mem.empty(num_buffers * numel + self._pad_bytes // 2, dtype=dtype, device=device)
         self.handle = symm_mem.rendezvous(self.storage, group)
         self.storage.zero_()
         bufs = [int(p) for p in self.handle.buffer_ptrs]
-        pads = [int(p) for p in self.handle.signal_pad_ptrs]
+        pads = [p + num_buffers * numel * 2 for p in bufs]
         self._bufs = (C.c_uint64 * self.world)(*bufs)
         self._pads = (C.c_uint64 * self.world)(*pads)
-        self._pad_bytes = int(self.handle.signal_pad_size)
         # NVLS: the multicast mapping of the same allocation (0 = no multicast support on this fabric / disabled)
         # B200_NVLS: "auto" (default) = above 4 ranks only - measured on B200 (profiles/r02_allreduce.md): at 2 ranks
         # one multimem.ld_reduce pass costs 13.6 us against 12.2 us for plain peer loads, at 8 ranks it replaces 7 MB

@@ -420,6 +420,38 @@ int b200_nvls_all_reduce_rms_norm_quant(void* result, float* scales, uint64_t mu
                                         const void* weight, void* residual, float epsilon, int64_t num_tokens,
                                         int hidden, int dtype, b200_stream_t stream);
 
+/* Barrier-free ("Lamport") all-reduce over peer memory: a pushed datum is its own arrival flag (receive buffers are
+ * pre-filled with a sentinel no pushed word can have), so a shot costs ONE one-way NVLink latency instead of a
+ * release + flag handshake (profiles/r02_allreduce.md).  One-shot up to 4 ranks, two-shot (reduce-scatter push, then
+ * all-gather push) above.  Reference analogue: FlashInfer trtllm_allreduce_fusion behind
+ * vllm/distributed/device_communicators/flashinfer_all_reduce.py and compilation/passes/fusion/allreduce_rms_fusion.py.
+ *   workspace: one region per rank of b200_lamport_workspace_bytes(world, max_numel) bytes, mapped into every rank
+ *     (torch symmetric memory), initialised ONCE with b200_lamport_workspace_init followed by a cross-rank barrier;
+ *     peer_workspaces[q] = rank q's region as addressable from this rank.  The call counter lives in the workspace
+ *     (device memory), so captured CUDA graphs replay correctly.  All ranks must issue the same sequence of calls.
+ *   input: this rank's [rows][cols] partial sums in ordinary local memory (cols % (8 * world_size) == 0);
+ *   out:   the sum (fp32 accumulation in rank order, rounded once - same values as b200_peer_all_reduce_out), local.
+ *   _rms_norm_quant: residual += sum; result, scales = per-token FP8 quant of RMSNorm(residual) * weight, bit-identical
+ *     to the all-reduce followed by b200_rms_norm_dynamic_per_token_quant.
+ * rank == -1 emulates all ranks on one GPU (tests), as for the entries above; input / out / residual / result then
+ * hold world_size copies rows * cols elements apart (scales: rows apart). */
+/*   _rms_norm_nvfp4_quant: the same with the NVFP4 quantiser (swizzled scales, padding written), bit-identical to the
+ *     all-reduce followed by b200_rms_norm_nvfp4_quant. */
+int64_t b200_lamport_workspace_bytes(int world_size, int64_t max_numel);
+int b200_lamport_workspace_init(void* workspace, int64_t workspace_bytes, b200_stream_t stream);
+int b200_lamport_all_reduce(void* out, const void* input, const uint64_t* peer_workspaces, int64_t workspace_bytes,
+                            int rank, int world_size, int64_t rows, int cols, int dtype, b200_stream_t stream);
+int b200_lamport_all_reduce_rms_norm_quant(void* result, float* scales, const void* input,
+                                           const uint64_t* peer_workspaces, int64_t workspace_bytes, int rank,
+                                           int world_size, const void* weight, void* residual, float epsilon,
+                                           int64_t num_tokens, int hidden, int dtype, b200_stream_t stream);
+
+int b200_lamport_all_reduce_rms_norm_nvfp4_quant(void* result, void* result_block_scale, const void* input,
+                                                 const uint64_t* peer_workspaces, int64_t workspace_bytes, int rank,
+                                                 int world_size, const void* weight, void* residual,
+                                                 const float* input_global_scale, float epsilon, int64_t num_tokens,
+                                                 int hidden, int dtype, b200_stream_t stream);
+
 /* Spin budget of one cross-rank barrier wait, in polls (default 2^28, minutes); 0 = wait for ever.  A rank
  * that exceeds it prints a message and traps instead of hanging the GPU. */
 void b200_peer_set_barrier_timeout(unsigned long long max_polls);

@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """All-reduce of the decode step's row-parallel output: NCCL vs the b200 peer-memory / NVLS kernels, each captured
 32x into a CUDA graph and replayed; max over ranks.  Sizes: 128 x 4096 bf16 = 1 MB (configs[2]) and 256 x 8192 bf16 =
-4 MB (configs[3]).  Run under torchrun:
+4 MB (configs[3]).  "lamport": all_reduce_out / the fused form through the barrier-free protocol (for it "one_shot_us"
+is the out-of-place all-reduce, one-shot up to 4 ranks and two-shot above).  Run under torchrun:
     python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 scripts/bench_allreduce.py [--json F]"""
 import json, os, sys
 from pathlib import Path
@@ -64,10 +65,12 @@ for B, H in ((128, 4096), (256, 8192)):
     def fused():
         par.all_reduce_rms_norm_quant(flip[0], B, w, 1e-5, resid); flip[0] ^= 1
 
-    for name, mc in (("peer", 0), ("nvls", mc_real)):
-        if name == "nvls" and not mc_real:
+    has_lp = par.lamport
+    for name, mc, lp in (("peer", 0, False), ("nvls", mc_real, False), ("lamport", 0, True)):
+        if (name == "nvls" and not mc_real) or (lp and not has_lp):
             continue
         par.multicast_ptr = mc
+        par.lamport = lp
         # correctness of each form first
         par.view(0, B, H).copy_(x); par.view(1, B, H).copy_(x); torch.cuda.synchronize(); dist.barrier()
         par.all_reduce_(0); torch.cuda.synchronize()
@@ -83,10 +86,11 @@ for B, H in ((128, 4096), (256, 8192)):
                         and torch.equal(rf, rr))
         ok = torch.tensor([int(fused_ok)], device=dev); dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         torch.cuda.synchronize(); dist.barrier()
-        r[name] = {"two_shot_us": timed(lambda: par.all_reduce_(0)), "one_shot_us": timed(one),
+        r[name] = {"two_shot_us": None if lp else timed(lambda: par.all_reduce_(0)), "one_shot_us": timed(one),
                    "fused_norm_quant_us": timed(fused), "err_two_shot": e2, "err_one_shot": e1,
                    "fused_bit_identical_all_ranks": bool(ok.item())}
     par.multicast_ptr = mc_real
+    par.lamport = has_lp
     # what the fused kernel replaces when the reduce is not fused: the stand-alone norm + quant kernel
     hid = torch.randn(B, H, device=dev).to(torch.bfloat16)
     r["rms_norm_quant_alone_us"] = timed(lambda: ops.rms_norm_dynamic_per_token_quant(hid, w, 1e-5, residual=resid))

@@ -104,9 +104,116 @@ def test_emulated_all_reduce_rms_norm_quant(cuda_lib, world):
             assert torch.equal(resid[r], res_ref)
 
 
+def _lamport_ws(world, max_numel, dev, lib):
+    from vllm_b200 import _lib
+
+    nbytes = int(lib.b200_lamport_workspace_bytes(world, max_numel))
+    ws = [torch.empty(nbytes, dtype=torch.uint8, device=dev) for _ in range(world)]
+    st = torch.cuda.current_stream(dev).cuda_stream
+    for w in ws:
+        _lib.check(lib.b200_lamport_workspace_init(w.data_ptr(), nbytes, st), "lamport_workspace_init")
+    return ws, nbytes, (C.c_uint64 * world)(*[w.data_ptr() for w in ws])
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_emulated_lamport_all_reduce(cuda_lib, world):
+    """Barrier-free all-reduce (one-shot up to 4 ranks, two-shot at 8), emulated ranks on one GPU: 10 calls in a row
+    (every receive-buffer generation is reused three times) with CHANGING message shapes, words that equal the
+    sentinel pattern in the inputs, exact against the fp32 sum rounded once."""
+    from vllm_b200 import _lib
+
+    dev = torch.device("cuda", 0)
+    H = 1024
+    ws, nbytes, tab = _lamport_ws(world, 64 * H, dev, cuda_lib)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    g = torch.Generator(device=dev).manual_seed(3)
+    for it, B in enumerate([48, 64, 7, 64, 1, 33, 64, 64, 5, 48]):
+        xs = torch.randn(world, B, H, device=dev, generator=g).to(torch.bfloat16)
+        xs[:, 0, :16] = -0.0   # sentinel words (pairs of -0) in every rank's message
+        xs[0, B - 1, 8:24] = -0.0
+        ref = xs.float().sum(0).to(torch.bfloat16)
+        out = torch.full((world, B, H), float("nan"), dtype=torch.bfloat16, device=dev)
+        rc = cuda_lib.b200_lamport_all_reduce(out.data_ptr(), xs.data_ptr(), tab, nbytes, -1, world, B, H, 2, st)
+        _lib.check(rc, "lamport_all_reduce(emu)")
+        torch.cuda.synchronize()
+        for r in range(world):
+            assert torch.equal(out[r], ref), (it, B, r)   # -0 == +0 under torch.equal: sign of zero is the documented caveat
+    # a message that does not fit the workspace is rejected before launch
+    big = torch.zeros(world, 65, H, dtype=torch.bfloat16, device=dev)
+    rc = cuda_lib.b200_lamport_all_reduce(big.data_ptr(), big.data_ptr(), tab, nbytes, -1, world, 65, H, 2, st)
+    assert rc != 0
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_emulated_lamport_all_reduce_rms_norm_quant(cuda_lib, world):
+    """Fused Lamport all-reduce + residual add + RMSNorm + per-token FP8 quant == all-reduce then the stand-alone
+    fused norm/quant kernel, bit for bit; more rows than CTAs (two rows per CTA) in some calls."""
+    from vllm_b200 import _lib, ops
+
+    dev = torch.device("cuda", 0)
+    H = 2048
+    ws, nbytes, tab = _lamport_ws(world, 80 * H, dev, cuda_lib)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    g = torch.Generator(device=dev).manual_seed(9)
+    w = (torch.rand(H, device=dev, generator=g) + 0.5).to(torch.bfloat16)
+    for it, B in enumerate([40, 80, 3, 80, 40, 17, 40]):
+        xs = torch.randn(world, B, H, device=dev, generator=g).to(torch.bfloat16)
+        res = torch.randn(B, H, device=dev, generator=g).to(torch.bfloat16)
+        summed = xs.float().sum(0).to(torch.bfloat16)
+        res_ref = res.clone()
+        xq_ref, xs_ref = ops.rms_norm_dynamic_per_token_quant(summed, w, 1e-5, residual=res_ref)
+        xq = torch.empty(world, B, H, dtype=torch.float8_e4m3fn, device=dev)
+        sc = torch.empty(world, B, dtype=torch.float32, device=dev)
+        resid = res.unsqueeze(0).repeat(world, 1, 1).contiguous()
+        rc = cuda_lib.b200_lamport_all_reduce_rms_norm_quant(xq.data_ptr(), sc.data_ptr(), xs.data_ptr(), tab, nbytes, -1,
+                                                             world, w.data_ptr(), resid.data_ptr(), 1e-5, B, H, 2, st)
+        _lib.check(rc, "lamport_all_reduce_rms_norm_quant(emu)")
+        torch.cuda.synchronize()
+        for r in range(world):
+            assert torch.equal(xq[r].view(torch.uint8), xq_ref.view(torch.uint8)), (it, B, r)
+            assert torch.equal(sc[r], xs_ref.reshape(-1))
+            assert torch.equal(resid[r], res_ref)
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_emulated_lamport_all_reduce_rms_norm_nvfp4_quant(cuda_lib, world):
+    """Fused Lamport all-reduce + residual add + RMSNorm + NVFP4 quant == all-reduce, then b200_rms_norm_nvfp4_quant,
+    bit for bit (codes, swizzled scales incl. the zeroed padding, residual)."""
+    from vllm_b200 import _lib, ops
+
+    dev = torch.device("cuda", 0)
+    H = 1024
+    ws, nbytes, tab = _lamport_ws(world, 140 * H, dev, cuda_lib)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    g = torch.Generator(device=dev).manual_seed(21)
+    w = (torch.rand(H, device=dev, generator=g) + 0.5).to(torch.bfloat16)
+    gs = torch.tensor([448.0 * 6.0 / 8.0], device=dev)
+    for it, B in enumerate([40, 130, 3, 140]):
+        xs = torch.randn(world, B, H, device=dev, generator=g).to(torch.bfloat16)
+        res = torch.randn(B, H, device=dev, generator=g).to(torch.bfloat16)
+        summed = xs.float().sum(0).to(torch.bfloat16)
+        res_ref = res.clone()
+        q_ref, sf_ref = ops.rms_norm_nvfp4_quant(summed, w, 1e-5, gs, residual=res_ref)
+        rows_pad, sf_cols = (B + 127) // 128 * 128, (H // 16 + 3) // 4 * 4
+        q = torch.empty(world, B, H // 2, dtype=torch.uint8, device=dev)
+        sf = torch.full((world, rows_pad, sf_cols), 0x55, dtype=torch.uint8, device=dev)
+        resid = res.unsqueeze(0).repeat(world, 1, 1).contiguous()
+        rc = cuda_lib.b200_lamport_all_reduce_rms_norm_nvfp4_quant(
+            q.data_ptr(), sf.data_ptr(), xs.data_ptr(), tab, nbytes, -1, world, w.data_ptr(), resid.data_ptr(),
+            gs.data_ptr(), 1e-5, B, H, 2, st)
+        _lib.check(rc, "lamport_all_reduce_rms_norm_nvfp4_quant(emu)")
+        torch.cuda.synchronize()
+        for r in range(world):
+            assert torch.equal(q[r], q_ref), (it, B, r)
+            assert torch.equal(sf[r].flatten(), sf_ref.view(torch.uint8).flatten()), (it, B, r)
+            assert torch.equal(resid[r], res_ref)
+
+
 # ------------------------------------------------------------------------------- real ranks
-def _worker(rank, world, port, q, nvls):
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), B200_NVLS="force" if nvls else "0")
+def _worker(rank, world, port, q, mode):
+    nvls = mode == "nvls"
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), B200_NVLS="force" if nvls else "0",
+                      B200_AR_LAMPORT="1" if mode == "lamport" else "0")
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
@@ -116,6 +223,7 @@ def _worker(rank, world, port, q, nvls):
     B, H = 48, 1024
     par = PeerAllReduce(dist.group.WORLD, dev, 2, B * H)
     used_nvls = bool(par.multicast_ptr)
+    assert par.lamport == (mode == "lamport")
     if nvls and not used_nvls and rank == 0:
         print("NVLS requested but the fabric exposes no multicast mapping: peer-load path tested instead", flush=True)
     g = torch.Generator(device=dev).manual_seed(7 + rank)
@@ -161,11 +269,12 @@ def _worker(rank, world, port, q, nvls):
     os._exit(0)
 
 
-@pytest.mark.parametrize("nvls", [True, False])
+@pytest.mark.parametrize("mode", ["lamport", "nvls", "peer"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_peer_all_reduce_real_ranks(world, nvls):
-    """nvls=True: multimem.ld_reduce (in-switch sum) when torch's symmetric memory exposes a multicast mapping;
-    nvls=False: the peer-load kernels (B200_NVLS=0)."""
+def test_peer_all_reduce_real_ranks(world, mode):
+    """lamport: the barrier-free protocol (default); nvls: multimem.ld_reduce / multimem.st (in-switch sum) when
+    torch's symmetric memory exposes a multicast mapping; peer: the flag-barrier peer-load kernels."""
+    nvls = mode
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     with socket.socket() as s:
@@ -173,11 +282,11 @@ def test_peer_all_reduce_real_ranks(world, nvls):
         port = s.getsockname()[1]
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, q, nvls)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q, mode)) for r in range(world)]
     for p in procs:
         p.start()
     ok, used_nvls = q.get(timeout=300)
     for p in procs:
         p.join(timeout=60)
-    print(f"world {world}: nvls requested {nvls}, used {used_nvls}")
+    print(f"world {world}: mode {mode}, nvls used {used_nvls}")
     assert ok

@@ -76,6 +76,11 @@ SIGNATURES: dict[str, tuple] = {
     "b200_nvls_all_reduce": (i32, [C.c_uint64, vp, vp, i32, i32, i64, i32, i64, i64, vp]),
     "b200_silu_and_mul_nvfp4_quant": (i32, [vp, vp, vp, vp, i32, i32, i32, vp]),
     "b200_rms_norm_nvfp4_quant": (i32, [vp, vp, vp, vp, vp, vp, i32, i32, i64, f32, i32, vp]),
+    "b200_lamport_workspace_bytes": (i64, [i32, i64]),
+    "b200_lamport_workspace_init": (i32, [vp, i64, vp]),
+    "b200_lamport_all_reduce": (i32, [vp, vp, vp, i64, i32, i32, i64, i32, i32, vp]),
+    "b200_lamport_all_reduce_rms_norm_quant": (i32, [vp, vp, vp, vp, i64, i32, i32, vp, vp, f32, i64, i32, i32, vp]),
+    "b200_lamport_all_reduce_rms_norm_nvfp4_quant": (i32, [vp, vp, vp, vp, i64, i32, i32, vp, vp, vp, f32, i64, i32, i32, vp]),
     "b200_nvls_all_reduce_out": (i32, [vp, C.c_uint64, vp, vp, i32, i32, i64, i32, i64, i64, vp]),
     "b200_nvls_all_reduce_rms_norm_quant": (i32, [vp, vp, C.c_uint64, vp, vp, i32, i32, i64, i64, vp, vp, f32, i64, i32,
                                                   i32, vp]),

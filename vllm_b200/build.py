@@ -34,6 +34,7 @@ SOURCES = [
     "gemm_persist.cu",
     "nvfp4_gemm.cu",
     "peer_allreduce.cu",
+    "lamport_allreduce.cu",
 ]
 
 NVCC_FLAGS = [

@@ -193,7 +193,7 @@ class DecodeRunner:
             return self._all_reduce(self._mm_fp4(xq, xsf, lw))
         out = self.par.view(which, self.B, self.s.hidden)
         self._mm_fp4(xq, xsf, lw, out=out)
-        if self.tp <= 4 and not self.par.multicast_ptr:
+        if self.par.lamport or (self.tp <= 4 and not self.par.multicast_ptr):
             return self.par.all_reduce_out(which, torch.empty_like(out))
         self.par.all_reduce_(which)  # two-shot, in place (through the switch when the fabric has multicast)
         return out
@@ -205,7 +205,7 @@ class DecodeRunner:
             return self._all_reduce(self._linear(x, lw))
         out = self.par.view(which, self.B, self.s.hidden)
         self._linear(x, lw, out=out)
-        if self.tp <= 4 or self.par.multicast_ptr:
+        if self.tp <= 4 or self.par.lamport:
             return self.par.all_reduce_out(which, torch.empty_like(out))
         self.par.all_reduce_(which)
         return out
@@ -240,7 +240,7 @@ class DecodeRunner:
         self._mm_fp8(xq, xs, lw, out=out)
         # one-shot (start barrier only; o/down alternate buffers): NVLS in-switch sum at any TP when the fabric has
         # multicast, else (tp-1) MB of peer reads, which beat a second cross-GPU barrier up to TP 4
-        if self.tp <= 4 or self.par.multicast_ptr:
+        if self.tp <= 4 or self.par.lamport:
             return self.par.all_reduce_out(which, torch.empty_like(out))
         self.par.all_reduce_(which)
         return out
@@ -254,7 +254,10 @@ class DecodeRunner:
         # TP <= 4: the all-reduce after a row-parallel GEMM is fused with the residual add + RMSNorm + FP8 quant
         # that follows it (b200_peer_all_reduce_rms_norm_quant); `pending` = the down_proj partial sums of the
         # previous layer still sit un-reduced in peer buffer 1
-        fuse_ar = fused and self.par is not None and (self.tp <= 4 or bool(self.par.multicast_ptr))
+        # (measured, profiles/r02_allreduce.md: at 8 ranks the fused forms lose to the in-place two-shot reduce
+        # followed by the separate norm + quant kernel - 4.08 vs 3.79 ms/step - unless the barrier-free Lamport
+        # protocol is on, which fuses at any TP)
+        fuse_ar = fused and self.par is not None and (self.tp <= 4 or self.par.lamport)
         pending = False
         fused4 = self.wq == "nvfp4" and self.fused
         for lw, kv in zip(self.layers, self.kv_caches):
@@ -264,9 +267,14 @@ class DecodeRunner:
                 # (+ all-reduce), norm+quant, GEMM, silu*mul+quant, GEMM (+ all-reduce)
                 for name in ("qkv", "o", "gate_up", "down"):
                     self._fp4_consts(lw[name])
+                fuse4_ar = self.par is not None and self.par.lamport
                 xq, xsf = self._fp4_bufs(B, s.hidden)
-                ops.rms_norm_nvfp4_quant(hidden, lw["ln1"], s.rms_eps, lw["qkv"]["ags"], residual=residual, result=xq,
-                                         result_block_scale=xsf)
+                if pending:  # the previous layer's down_proj partial sums are still un-reduced in peer buffer 1
+                    self.par.all_reduce_rms_norm_nvfp4_quant(1, B, lw["ln1"], s.rms_eps, residual, lw["qkv"]["ags"],
+                                                             result=xq, result_block_scale=xsf)
+                else:
+                    ops.rms_norm_nvfp4_quant(hidden, lw["ln1"], s.rms_eps, lw["qkv"]["ags"], residual=residual,
+                                             result=xq, result_block_scale=xsf)
                 qkv = self._mm_fp4(xq, xsf, lw["qkv"])
                 q, k, v = qkv.split([self.Hq * self.D, self.Hkv * self.D, self.Hkv * self.D], dim=-1)
                 ops.rotary_embedding_and_cache_write(self.positions, q, k, v, self.D, self.cos_sin, kc, vc,
@@ -276,14 +284,23 @@ class DecodeRunner:
                                            self.v_scale, num_splits=self.num_splits, workspace=self.attn_ws)
                 oq, osf = self._fp4_bufs(B, self.Hq * self.D)
                 ops.scaled_fp4_quant_out(attn_out.view(B, -1), lw["o"]["ags"], True, oq, osf)
-                hidden = self._reduce_fp4(oq, osf, lw["o"], 0)
                 xq, xsf = self._fp4_bufs(B, s.hidden)
-                ops.rms_norm_nvfp4_quant(hidden, lw["ln2"], s.rms_eps, lw["gate_up"]["ags"], residual=residual,
-                                         result=xq, result_block_scale=xsf)
+                if fuse4_ar:  # o_proj partial sums -> peer buffer 0 -> all-reduce + add + RMSNorm + NVFP4 quant
+                    self._mm_fp4(oq, osf, lw["o"], out=self.par.view(0, B, s.hidden))
+                    self.par.all_reduce_rms_norm_nvfp4_quant(0, B, lw["ln2"], s.rms_eps, residual, lw["gate_up"]["ags"],
+                                                             result=xq, result_block_scale=xsf)
+                else:
+                    hidden = self._reduce_fp4(oq, osf, lw["o"], 0)
+                    ops.rms_norm_nvfp4_quant(hidden, lw["ln2"], s.rms_eps, lw["gate_up"]["ags"], residual=residual,
+                                             result=xq, result_block_scale=xsf)
                 gu = self._mm_fp4(xq, xsf, lw["gate_up"])
                 aq, asf = self._fp4_bufs(B, self.inter)
                 ops.silu_and_mul_nvfp4_quant(aq, asf, gu, lw["down"]["ags"])
-                hidden = self._reduce_fp4(aq, asf, lw["down"], 1)
+                if fuse4_ar:
+                    self._mm_fp4(aq, asf, lw["down"], out=self.par.view(1, B, s.hidden))
+                    pending = True
+                else:
+                    hidden = self._reduce_fp4(aq, asf, lw["down"], 1)
                 continue
             if fused:
                 # 10 launches per layer: norm+quant, GEMM, rope+cache, attention (+combine), quant, GEMM,

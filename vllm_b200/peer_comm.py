@@ -51,6 +51,21 @@ class PeerAllReduce:
                 mc = 0
         self.multicast_ptr = mc
         self._dt = 2 if dtype == torch.bfloat16 else 1  # B200_DT_BF16 / B200_DT_F16
+        # Barrier-free (Lamport) protocol: its own symmetric region (state + 3 generations of receive buffers,
+        # pre-filled with the sentinel).  B200_AR_LAMPORT: "1" (default) = used by all_reduce_out and
+        # all_reduce_rms_norm_quant, "0" = the flag-barrier kernels above.
+        self.lamport = False
+        if os.environ.get("B200_AR_LAMPORT", "1") not in ("0", "off"):
+            lib = _lib.load()
+            self._lp_bytes = int(lib.b200_lamport_workspace_bytes(self.world, numel))
+            self._lp_storage = symm_mem.empty((self._lp_bytes + 1) // 2, dtype=dtype, device=device)
+            self._lp_handle = symm_mem.rendezvous(self._lp_storage, group)
+            from .ops import _stream
+
+            _lib.check(lib.b200_lamport_workspace_init(self._lp_storage.data_ptr(), self._lp_bytes,
+                                                       _stream(self._lp_storage)), "lamport_workspace_init")
+            self._lp_ws = (C.c_uint64 * self.world)(*[int(p) for p in self._lp_handle.buffer_ptrs])
+            self.lamport = True
         torch.cuda.synchronize(device)
         dist.barrier(group)
 
@@ -70,6 +85,13 @@ class PeerAllReduce:
 
         if out.numel() != self.numel or out.dtype != self.dtype or not out.is_contiguous():
             raise RuntimeError("PeerAllReduce.all_reduce_out: out must be a contiguous tensor of the buffer's size/dtype")
+        if self.lamport:
+            cols = out.shape[-1] if out.dim() >= 2 and out.shape[-1] % (8 * self.world) == 0 else 8 * self.world
+            src = self.storage[index * self.numel:(index + 1) * self.numel]
+            rc = _lib.load().b200_lamport_all_reduce(out.data_ptr(), src.data_ptr(), self._lp_ws, self._lp_bytes, self.rank,
+                                                     self.world, self.numel // cols, cols, self._dt, _stream(self.storage))
+            _lib.check(rc, "lamport_all_reduce")
+            return out
         if self.multicast_ptr:
             rc = _lib.load().b200_nvls_all_reduce_out(out.data_ptr(), self.multicast_ptr, self._bufs, self._pads, self.rank,
                                                       self.world, self.numel, self._dt, index * self.numel * 2,
@@ -93,6 +115,13 @@ class PeerAllReduce:
             raise RuntimeError("PeerAllReduce.all_reduce_rms_norm_quant: shapes do not match the buffer")
         xq = torch.empty(num_tokens, hidden, dtype=torch.float8_e4m3fn, device=residual.device)
         xs = torch.empty(num_tokens, 1, dtype=torch.float32, device=residual.device)
+        if self.lamport:
+            src = self.storage[index * self.numel:(index + 1) * self.numel]
+            rc = _lib.load().b200_lamport_all_reduce_rms_norm_quant(
+                xq.data_ptr(), xs.data_ptr(), src.data_ptr(), self._lp_ws, self._lp_bytes, self.rank, self.world,
+                weight.data_ptr(), residual.data_ptr(), float(epsilon), num_tokens, hidden, self._dt, _stream(self.storage))
+            _lib.check(rc, "lamport_all_reduce_rms_norm_quant")
+            return xq, xs
         if self.multicast_ptr:
             rc = _lib.load().b200_nvls_all_reduce_rms_norm_quant(
                 xq.data_ptr(), xs.data_ptr(), self.multicast_ptr, self._bufs, self._pads, self.rank, self.world,
@@ -106,6 +135,32 @@ class PeerAllReduce:
             _stream(self.storage))
         _lib.check(rc, "peer_all_reduce_rms_norm_quant")
         return xq, xs
+
+    def all_reduce_rms_norm_nvfp4_quant(self, index: int, num_tokens: int, weight: torch.Tensor, epsilon: float,
+                                        residual: torch.Tensor, global_scale: torch.Tensor,
+                                        result: torch.Tensor | None = None,
+                                        result_block_scale: torch.Tensor | None = None):
+        """residual += sum over ranks of buffer `index`; returns the NVFP4 quant (packed codes, swizzled scale buffer)
+        of RMSNorm(residual) * weight - one kernel (Lamport protocol only)."""
+        from .ops import _stream, round_up
+
+        if not self.lamport:
+            raise RuntimeError("PeerAllReduce.all_reduce_rms_norm_nvfp4_quant needs the Lamport protocol (B200_AR_LAMPORT)")
+        hidden = self.numel // num_tokens
+        if hidden * num_tokens != self.numel or residual.shape != (num_tokens, hidden) or not residual.is_contiguous():
+            raise RuntimeError("PeerAllReduce.all_reduce_rms_norm_nvfp4_quant: shapes do not match the buffer")
+        if result is None:
+            result = torch.empty(num_tokens, hidden // 2, dtype=torch.uint8, device=residual.device)
+        if result_block_scale is None:
+            result_block_scale = torch.empty(round_up(num_tokens, 128), round_up(hidden // 16, 4) // 4, dtype=torch.int32,
+                                             device=residual.device)
+        src = self.storage[index * self.numel:(index + 1) * self.numel]
+        rc = _lib.load().b200_lamport_all_reduce_rms_norm_nvfp4_quant(
+            result.data_ptr(), result_block_scale.data_ptr(), src.data_ptr(), self._lp_ws, self._lp_bytes, self.rank,
+            self.world, weight.data_ptr(), residual.data_ptr(), global_scale.data_ptr(), float(epsilon), num_tokens, hidden,
+            self._dt, _stream(self.storage))
+        _lib.check(rc, "lamport_all_reduce_rms_norm_nvfp4_quant")
+        return result, result_block_scale
 
     def all_reduce_(self, index: int) -> None:
         """Sum buffer `index` over the ranks, in place, on the current stream."""

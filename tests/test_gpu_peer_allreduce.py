@@ -175,14 +175,13 @@ def test_emulated_lamport_all_reduce_rms_norm_quant(cuda_lib, world):
             assert torch.equal(resid[r], res_ref)
 
 
-@pytest.mark.parametrize("world", [2, 8])
-def test_emulated_lamport_all_reduce_rms_norm_nvfp4_quant(cuda_lib, world):
+@pytest.mark.parametrize("world,H", [(2, 1024), (8, 1024), (2, 8192), (8, 8192)])
+def test_emulated_lamport_all_reduce_rms_norm_nvfp4_quant(cuda_lib, world, H):
     """Fused Lamport all-reduce + residual add + RMSNorm + NVFP4 quant == all-reduce, then b200_rms_norm_nvfp4_quant,
     bit for bit (codes, swizzled scales incl. the zeroed padding, residual)."""
     from vllm_b200 import _lib, ops
 
     dev = torch.device("cuda", 0)
-    H = 1024
     ws, nbytes, tab = _lamport_ws(world, 140 * H, dev, cuda_lib)
     st = torch.cuda.current_stream(dev).cuda_stream
     g = torch.Generator(device=dev).manual_seed(21)

@@ -303,9 +303,10 @@ __global__ void __launch_bounds__(1024) lamport_all_reduce_rms_norm_quant_kernel
 // ---- fused with the NVFP4 consumer: residual += sum; (codes, swizzled scales) = NVFP4 quant of RMSNorm(residual) * w ----
 // Bit-identical to the all-reduce followed by b200_rms_norm_nvfp4_quant (= fused_add_rms_norm + scaled_fp4_quant):
 // the sum and the residual add are each rounded to T, and the variance is summed in rms_norm_kernel's element order,
-// which is why this kernel always runs 256 threads.  Scale rows of the 128-row padding are zeroed here too.
+// which is why only threads 0..255 take part in that sum (pushes, polls and the quantiser use the whole block).
+// Scale rows of the 128-row padding are zeroed here too.
 template <typename T>
-__global__ void __launch_bounds__(256) lamport_all_reduce_rms_norm_nvfp4_quant_kernel(
+__global__ void __launch_bounds__(1024) lamport_all_reduce_rms_norm_nvfp4_quant_kernel(
     const LpArgs a, const T* in, uint32_t* out, uint8_t* sf_out, const T* __restrict__ w, T* residual,
     const float* __restrict__ global_scale, float eps, int64_t emu_stride, int64_t emu_sf_stride) {
   pdl_trigger();
@@ -350,10 +351,11 @@ __global__ void __launch_bounds__(256) lamport_all_reduce_rms_norm_nvfp4_quant_k
       [&](int row) {
         __syncthreads();
         float ss = 0.f;
-        for (int e = threadIdx.x; e < hidden; e += blockDim.x) ss += rowf[e] * rowf[e];
+        if (threadIdx.x < 256)  // rms_norm_kernel's element-to-thread map (256 threads, stride 256)
+          for (int e = threadIdx.x; e < hidden; e += 256) ss += rowf[e] * rowf[e];
         ss = warp_sum(ss);
         const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-        if (lane == 0) sh[warp] = ss;
+        if (lane == 0 && warp < 8) sh[warp] = ss;
         __syncthreads();
         ss = warp_sum(lane < 8 ? sh[lane] : 0.f);
         const float inv = rsqrtf(ss / hidden + eps);
@@ -542,7 +544,8 @@ extern "C" int b200_lamport_all_reduce_rms_norm_nvfp4_quant(void* result, void* 
     using T = decltype(tag);
     if (int rc_attr = ensure_dyn_smem(reinterpret_cast<const void*>(lamport_all_reduce_rms_norm_nvfp4_quant_kernel<T>), 32768 * 4))
       return rc_attr;
-    launch_kernel_ex(lamport_all_reduce_rms_norm_nvfp4_quant_kernel<T>, g, dim3(256), (size_t)hidden * 4, s, 1, a.emu != 0, a,
+    const int threads = lp_threads(hidden / 8) < 256 ? 256 : lp_threads(hidden / 8);
+    launch_kernel_ex(lamport_all_reduce_rms_norm_nvfp4_quant_kernel<T>, g, dim3(threads), (size_t)hidden * 4, s, 1, a.emu != 0, a,
                      (const T*)input, (uint32_t*)result, (uint8_t*)result_block_scale, (const T*)weight, (T*)residual,
                      input_global_scale, epsilon, stride, sf_stride);
     B200_CHECK_LAUNCH();

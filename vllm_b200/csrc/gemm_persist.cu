@@ -351,174 +351,9 @@ __global__ void __launch_bounds__(kP2Threads, 1)
   if (threadIdx.x == 0) p2_stamp(g, 10);
 }
 
-// ---------------------------------------------------------------------------------------------------------
-// Decode regime (M <= 256) on the same pair structure, with the two operands in SEPARATE rings.
-// The weights stream from HBM once and nothing else does: what bounds the kernel is how many weight bytes each SM
-// keeps in flight (HBM latency ~2 us x 6.5 TB/s = ~13 MB over the chip).  With one combined ring half (BN = 128) or
-// two thirds (BN = 64) of every stage is the token tile, which comes from L2 and needs no depth.  Here the token
-// ring has 4 slots and the weight ring takes the rest of shared memory (BN = 128: 21 x 8 KB, BN = 64: 32 x 4 KB
-// per CTA at UM = 128), its producer never waits for the preceding kernel (the weights do not depend on it:
-// programmatic dependent launch lets the ring fill while the predecessor drains), and no K split and no fix-up
-// are needed because a pair streams a whole K row block.  Warps: 0 weight producer, 1 TMEM alloc + MMA (leader),
-// 2-9 epilogue, 10 token producer.
-constexpr int kD2Threads = 352;
-
-template <int UM, int BN> struct D2Cfg {
-  static constexpr int A_ROWS = UM / 2;
-  static constexpr int A_BYTES = A_ROWS * kP2BK;
-  static constexpr int B_BYTES = (BN / 2) * kP2BK;
-  static constexpr int A_STAGES = 4;
-  static constexpr int B_FIT = (200 * 1024 - A_STAGES * A_BYTES) / B_BYTES;
-  static constexpr int B_STAGES = B_FIT > 32 ? 32 : B_FIT;
-  static constexpr int ACC_COLS = UM == 256 ? BN : BN / 2;
-  static constexpr int TMEM_COLS =
-      2 * ACC_COLS <= 32 ? 32 : (2 * ACC_COLS <= 64 ? 64 : (2 * ACC_COLS <= 128 ? 128 : (2 * ACC_COLS <= 256 ? 256 : 512)));
-  static constexpr int BAR_BYTES = (2 * A_STAGES + 2 * B_STAGES + 4) * 8 + 16;
-  static constexpr int SMEM_BYTES = A_STAGES * A_BYTES + B_STAGES * B_BYTES + 1024 /*align*/ + 1024 /*barriers*/;
-  static_assert(BAR_BYTES <= 1024, "barrier area");
-};
-
-template <int UM, int BN, typename OutT>
-__global__ void __launch_bounds__(kD2Threads, 1)
-    fp8_gemm_2sm_decode_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                               const P2Args g) {
-  using Cfg = D2Cfg<UM, BN>;
-  constexpr int AS = Cfg::A_STAGES, BS = Cfg::B_STAGES;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = align_smem_1024(smem_raw);
-  uint8_t* ring_a = smem;
-  uint8_t* ring_b = smem + AS * Cfg::A_BYTES;
-  uint64_t* full_a = reinterpret_cast<uint64_t*>(ring_b + BS * Cfg::B_BYTES);
-  uint64_t* empty_a = full_a + AS;
-  uint64_t* full_b = empty_a + AS;
-  uint64_t* empty_b = full_b + BS;
-  uint64_t* tmem_full_bar = empty_b + BS;        // [2]
-  uint64_t* tmem_empty_bar = tmem_full_bar + 2;  // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int rank = (int)p2_cluster_ctarank();
-  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
-  const int num_tiles = g.tiles_m * g.tiles_n;
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < AS; ++s) {
-      mbar_init(&full_a[s], 1);  // the leader's arrive.expect_tx covers both CTAs' bytes
-      mbar_init(&empty_a[s], 1);
-    }
-    for (int s = 0; s < BS; ++s) {
-      mbar_init(&full_b[s], 1);
-      mbar_init(&empty_b[s], 1);
-    }
-    for (int b = 0; b < 2; ++b) {
-      mbar_init(&tmem_full_bar[b], 1);
-      mbar_init(&tmem_empty_bar[b], 16);
-    }
-    fence_barrier_init();
-    prefetch_tensormap(&tmap_a);
-    prefetch_tensormap(&tmap_b);
-  }
-  if (warp == 1) tmem_alloc_2sm<Cfg::TMEM_COLS>(tmem_slot);
-  umma::fence_before_sync();
-  p2_cluster_sync();
-  umma::fence_after_sync();
-  const uint32_t tmem_base = *tmem_slot;
-  pdl_trigger();
-
-  if (warp == 0) {
-    // ===== weight producer (both CTAs): my BN/2 rows of every k-block of every tile of this pair; never waits
-    // for the preceding kernel =====
-    if (umma::elect_one()) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = pair; t < num_tiles; t += num_pairs) {
-        const int b_row = (t / g.tiles_m) * BN + rank * (BN / 2);
-        for (int kb = 0; kb < g.num_kb; ++kb) {
-          mbar_wait(&empty_b[stage], phase ^ 1);
-          if (rank == 0) mbar_arrive_expect_tx(&full_b[stage], 2 * Cfg::B_BYTES);
-          tma_load_2d_2sm(ring_b + stage * Cfg::B_BYTES, &tmap_b, &full_b[stage], kb * kP2BK, b_row, kEvictFirst);
-          if (++stage == BS) {
-            stage = 0;
-            phase ^= 1;
-          }
-        }
-      }
-    }
-  } else if (warp == 10) {
-    // ===== token producer (both CTAs): my UM/2 rows, from L2 after the first pair has pulled them in =====
-    if (umma::elect_one()) {
-      pdl_wait();  // the activations are the preceding kernel's output
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = pair; t < num_tiles; t += num_pairs) {
-        const int a_row = (t % g.tiles_m) * UM + rank * Cfg::A_ROWS;
-        for (int kb = 0; kb < g.num_kb; ++kb) {
-          mbar_wait(&empty_a[stage], phase ^ 1);
-          if (rank == 0) mbar_arrive_expect_tx(&full_a[stage], 2 * Cfg::A_BYTES);
-          tma_load_2d_2sm(ring_a + stage * Cfg::A_BYTES, &tmap_a, &full_a[stage], kb * kP2BK, a_row, kEvictLast);
-          if (++stage == AS) {
-            stage = 0;
-            phase ^= 1;
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===== MMA issuer (leader CTA only) =====
-    if (rank == 0 && umma::elect_one()) {
-      constexpr uint32_t idesc = umma::make_idesc_f8(UM, BN);
-      int sa = 0, sb = 0;
-      uint32_t pa = 0, pb = 0;
-      int it = 0;
-      for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
-        const int acc = it & 1;
-        mbar_wait(&tmem_empty_bar[acc], (((uint32_t)it >> 1) & 1) ^ 1);
-        umma::fence_after_sync();
-        const uint32_t tacc = tmem_base + acc * Cfg::ACC_COLS;
-        for (int kb = 0; kb < g.num_kb; ++kb) {
-          mbar_wait(&full_b[sb], pb);
-          mbar_wait(&full_a[sa], pa);
-          umma::fence_after_sync();
-          const uint64_t da = umma::make_desc_k_sw128(smem_u32(ring_a + sa * Cfg::A_BYTES));
-          const uint64_t db = umma::make_desc_k_sw128(smem_u32(ring_b + sb * Cfg::B_BYTES));
-#pragma unroll
-          for (int kk = 0; kk < kP2BK / 32; ++kk)
-            mma_f8f6f4_2sm(tacc, umma::desc_advance(da, kk * 32), umma::desc_advance(db, kk * 32), idesc,
-                           (kb | kk) != 0);
-          commit_2sm(&empty_a[sa]);  // each frees its slot in both CTAs
-          commit_2sm(&empty_b[sb]);
-          if (++sa == AS) {
-            sa = 0;
-            pa ^= 1;
-          }
-          if (++sb == BS) {
-            sb = 0;
-            pb ^= 1;
-          }
-        }
-        commit_2sm(&tmem_full_bar[acc]);
-      }
-    }
-  } else {
-    pdl_wait();  // scales, bias and the output buffer belong to the stream order from here
-    p2_epilogue<UM, BN, Cfg::ACC_COLS, OutT>(g, tmem_base, tmem_full_bar, tmem_empty_bar, warp, lane, rank, pair,
-                                            num_pairs);
-  }
-  umma::fence_before_sync();
-  p2_cluster_sync();
-  if (warp == 1) tmem_dealloc_2sm<Cfg::TMEM_COLS>(tmem_base);
-}
-
-template <int UM, int BN, typename OutT>
-static int launch_d2(const CUtensorMap& ta, const CUtensorMap& tb, const P2Args& g, int num_pairs, cudaStream_t stream) {
-  using Cfg = D2Cfg<UM, BN>;
-  auto kern = fp8_gemm_2sm_decode_kernel<UM, BN, OutT>;
-  if (int rc = ensure_dyn_smem(reinterpret_cast<const void*>(kern), Cfg::SMEM_BYTES)) return rc;
-  launch_kernel(kern, dim3(2 * num_pairs), dim3(kD2Threads), Cfg::SMEM_BYTES, stream, 2, ta, tb, g);
-  B200_CHECK_LAUNCH();
-  count_launch();
-  return 0;
-}
+// (A decode-regime variant with SEPARATE token / weight rings - 4 token slots, 21 weight slots - was built and
+// measured slower: the token tile's L2 round trip needs ring depth too.  Removed; see profiles/r02_gemm_decode_2sm.md
+// and commit 9f01e8b.)
 
 template <int UM, int BN, typename OutT>
 static int launch_p2(const CUtensorMap& ta, const CUtensorMap& tb, const P2Args& g, int num_pairs, cudaStream_t stream) {
@@ -533,7 +368,7 @@ static int launch_p2(const CUtensorMap& ta, const CUtensorMap& tb, const P2Args&
 
 static float* g_p2_dump = nullptr;
 
-template <int UM, int BN, typename OutT, bool kDecode = false>
+template <int UM, int BN, typename OutT>
 static int run_p2(P2Args g, const void* a, const void* b, int64_t lda, int64_t ldb, cudaStream_t stream) {
   g.tiles_m = (g.M + UM - 1) / UM;
   g.tiles_n = (g.N + BN - 1) / BN;
@@ -546,8 +381,7 @@ static int run_p2(P2Args g, const void* a, const void* b, int64_t lda, int64_t l
   const int tiles = g.tiles_m * g.tiles_n;
   int pairs = sm_count() / 2;
   if (pairs > tiles) pairs = tiles;
-  if constexpr (kDecode) return launch_d2<UM, BN, OutT>(ta, tb, g, pairs, stream);
-  else return launch_p2<UM, BN, OutT>(ta, tb, g, pairs, stream);
+  return launch_p2<UM, BN, OutT>(ta, tb, g, pairs, stream);
 }
 
 // Returns 1 when the shape is not handled here (the caller falls back), 0 on success, a negative B200_ERR_*
@@ -579,29 +413,14 @@ int run_fp8_gemm_2sm(void* out, const void* a, const void* b, const float* a_sca
     return (e && *e) ? atoi(e) : 0;
   }();
   if (M <= 256) {
-    // Decode regime: the weights stream once, every pair of SMs should be streaming.  One M tile (UMMA M = 128
-    // across the pair up to 128 tokens, else 256); the narrower weight tile when the wide one leaves SMs idle
-    // (o_proj / down_proj: N = 4096 -> 32 wide tiles for 74 pairs) or saves rounds of the persistent loop.
-    const long t128 = (N + 127) / 128, t64 = (N + 63) / 64;
-    const double cost128 = (double)((t128 + pairs - 1) / pairs), cost64 = 0.75 * (double)((t64 + pairs - 1) / pairs);
-    (void)cost64;
-    (void)cost128;
+    // Decode regime: the weights stream once.  One M tile (UMMA M = 128 across the pair up to 128 tokens, else 256).
+    const long t128 = (N + 127) / 128;
     // 64-wide tiles only when the wide ones would occupy under a quarter of the pairs (measured: o_proj N = 4096
     // 9.07 us with 32 wide tiles against 9.25-9.9 with 64 narrow ones - the narrow stage is 2/3 token bytes)
     const bool narrow = force_bn ? force_bn == 64 : t128 * 4 <= pairs;
-    static const bool split_rings = [] {
-      const char* e = getenv("B200_GEMM_DECODE_RINGS");  // 1 = the split-ring kernel (measured slower, see above)
-      return e && *e && atoi(e) != 0;
-    }();
-    if (!split_rings) {
-      if (M <= 128) return narrow ? run_p2<128, 64, OutT>(g, a, b, lda, ldb, stream) : run_p2<128, 128, OutT>(g, a, b, lda, ldb, stream);
-      return narrow ? run_p2<256, 64, OutT>(g, a, b, lda, ldb, stream) : run_p2<256, 128, OutT>(g, a, b, lda, ldb, stream);
-    }
     if (M <= 128)
-      return narrow ? run_p2<128, 64, OutT, true>(g, a, b, lda, ldb, stream)
-                    : run_p2<128, 128, OutT, true>(g, a, b, lda, ldb, stream);
-    return narrow ? run_p2<256, 64, OutT, true>(g, a, b, lda, ldb, stream)
-                  : run_p2<256, 128, OutT, true>(g, a, b, lda, ldb, stream);
+      return narrow ? run_p2<128, 64, OutT>(g, a, b, lda, ldb, stream) : run_p2<128, 128, OutT>(g, a, b, lda, ldb, stream);
+    return narrow ? run_p2<256, 64, OutT>(g, a, b, lda, ldb, stream) : run_p2<256, 128, OutT>(g, a, b, lda, ldb, stream);
   }
   // Tile width.  256 x 256 is the balanced tile (a k-block's 32 KB per SM arrive in about the time its four
   // 256x256x32 MMAs take); 256 x 128 halves the MMA work per k-block but still needs 24 KB, so it costs ~0.7 of a

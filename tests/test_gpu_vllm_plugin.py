@@ -235,6 +235,54 @@ def test_torch_ops_b200_run_on_cuda(plugin):
     torch.testing.assert_close(out.cpu().float(), ref, atol=2e-2, rtol=1e-2)
 
 
+def test_torch_ops_b200_fused_elementwise(plugin):
+    """The norm / activation / rope ops and their fused-quant forms through torch.ops.b200 (the reference's schemas,
+    torch_bindings.cpp:251-253,370-377,394-396,418-421,582) == the same kernels through vllm_b200.ops."""
+    from vllm_b200 import ops
+
+    g = torch.Generator().manual_seed(1)
+    M, Hd = 19, 512
+    x = torch.randn(M, Hd, generator=g).to(torch.bfloat16).to(DEV)
+    w = (torch.rand(Hd, generator=g) + 0.5).to(torch.bfloat16).to(DEV)
+    r = torch.randn(M, Hd, generator=g).to(torch.bfloat16).to(DEV)
+    out, ref = torch.empty_like(x), torch.empty_like(x)
+    torch.ops.b200.rms_norm(out, x, w, 1e-5)
+    ops.rms_norm(ref, x, w, 1e-5)
+    assert torch.equal(out, ref)
+    x1, r1, x2, r2 = x.clone(), r.clone(), x.clone(), r.clone()
+    torch.ops.b200.fused_add_rms_norm(x1, r1, w, 1e-5)
+    ops.fused_add_rms_norm(x2, r2, w, 1e-5)
+    assert torch.equal(x1, x2) and torch.equal(r1, r2)
+    q = torch.empty(M, Hd, dtype=torch.float8_e4m3fn, device=DEV)
+    sc = torch.empty(M, 1, device=DEV)
+    r3, r4 = r.clone(), r.clone()
+    torch.ops.b200.rms_norm_dynamic_per_token_quant(q, x, w, sc, 1e-5, None, r3)
+    q2, sc2 = ops.rms_norm_dynamic_per_token_quant(x, w, 1e-5, residual=r4)
+    assert torch.equal(q.view(torch.uint8), q2.view(torch.uint8)) and torch.equal(sc, sc2) and torch.equal(r3, r4)
+    gu = torch.randn(M, 2 * Hd, generator=g).to(torch.bfloat16).to(DEV)
+    a1, a2 = torch.empty(M, Hd, dtype=torch.bfloat16, device=DEV), torch.empty(M, Hd, dtype=torch.bfloat16, device=DEV)
+    torch.ops.b200.silu_and_mul(a1, gu)
+    ops.silu_and_mul(a2, gu)
+    assert torch.equal(a1, a2)
+    gs = torch.tensor([448.0 * 6.0 / 10.0], device=DEV)
+    c1, c2 = (torch.empty(M, Hd // 2, dtype=torch.uint8, device=DEV) for _ in range(2))
+    s1, s2 = (torch.zeros(128, Hd // 64, dtype=torch.int32, device=DEV) for _ in range(2))
+    torch.ops.b200.silu_and_mul_nvfp4_quant(c1, s1, gu, gs)
+    ops.silu_and_mul_nvfp4_quant(c2, s2, gu, gs)
+    assert torch.equal(c1, c2) and torch.equal(s1, s2)
+    T, Hq, D = 7, 4, 128
+    pos = torch.arange(T, device=DEV)
+    cs = torch.randn(64, D, generator=g).to(torch.bfloat16).to(DEV)
+    qk = torch.randn(T, 2 * Hq * D, generator=g).to(torch.bfloat16).to(DEV)
+    qa, ka = qk.clone()[:, :Hq * D], qk.clone()[:, Hq * D:]
+    qb, kb = qk.clone()[:, :Hq * D], qk.clone()[:, Hq * D:]
+    torch.ops.b200.rotary_embedding(pos, qa, ka, D, cs, True)
+    ops.rotary_embedding(pos, qb, kb, D, cs, True)
+    assert torch.equal(qa, qb) and torch.equal(ka, kb) and not torch.equal(qa, qk[:, :Hq * D])
+    with pytest.raises(RuntimeError):
+        torch.ops.b200.rotary_embedding(pos, qa, ka, D, cs, False)
+
+
 @pytest.mark.parametrize("kv_dtype", ["auto", "fp8"])
 @pytest.mark.parametrize("is_neox", [True, False])
 def test_fused_rope_kvcache_hook_matches_unfused(plugin, kv_dtype, is_neox):

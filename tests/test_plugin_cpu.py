@@ -90,6 +90,16 @@ REFERENCE_SCHEMAS = {
     "dynamic_scaled_fp8_quant": "dynamic_scaled_fp8_quant(Tensor! result, Tensor input, Tensor! scale) -> ()",
     "dynamic_per_token_scaled_fp8_quant": "dynamic_per_token_scaled_fp8_quant(Tensor! result, Tensor input, Tensor! scale, "
                                           "Tensor? scale_ub) -> ()",
+    # torch_bindings.cpp:370-377, 394-396, 418-421, 582, 251-253
+    "rms_norm": "rms_norm(Tensor! result, Tensor input, Tensor? weight, float epsilon) -> ()",
+    "fused_add_rms_norm": "fused_add_rms_norm(Tensor! input, Tensor! residual, Tensor? weight, float epsilon) -> ()",
+    "rms_norm_dynamic_per_token_quant": "rms_norm_dynamic_per_token_quant(Tensor! result, Tensor input, Tensor weight, "
+                                        "Tensor! scale, float epsilon, Tensor? scale_ub, Tensor!? residual) -> ()",
+    "rotary_embedding": "rotary_embedding(Tensor positions, Tensor! query, Tensor!? key, int head_size, "
+                        "Tensor cos_sin_cache, bool is_neox, int rope_dim_offset=0, bool inverse=False) -> ()",
+    "silu_and_mul": "silu_and_mul(Tensor! result, Tensor input) -> ()",
+    "silu_and_mul_nvfp4_quant": "silu_and_mul_nvfp4_quant(Tensor! result, Tensor! result_block_scale, Tensor input, "
+                                "Tensor input_global_scale) -> ()",
 }
 
 

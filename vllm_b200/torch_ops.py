@@ -14,6 +14,11 @@ tensor tracing (torch.compile / CUDA-graph capture in vLLM's piecewise mode) and
   dynamic_scaled_fp8_quant                torch_bindings.cpp:650-653
   dynamic_per_token_scaled_fp8_quant      torch_bindings.cpp:656-659
   merge_attn_states                       torch_bindings.cpp:354-362
+  rms_norm / fused_add_rms_norm           torch_bindings.cpp:370-377
+  rms_norm_dynamic_per_token_quant        torch_bindings.cpp:394-396
+  rotary_embedding                        torch_bindings.cpp:418-421 (neox layout only)
+  silu_and_mul                            torch_bindings.cpp:582
+  silu_and_mul_nvfp4_quant                torch_bindings.cpp:251-253
   paged_attention_decode                  (ours; the legacy paged_attention_v1/v2 ops only exist
                                            in the installed wheel, INSTALLED:_custom_ops.py:114-205)
 
@@ -51,6 +56,17 @@ SCHEMAS = {
         "(Tensor(a!) output, Tensor(b!)? output_lse, Tensor prefix_output, Tensor prefix_lse, "
         "Tensor suffix_output, Tensor suffix_lse, int? prefill_tokens_with_context=None, "
         "Tensor? output_scale=None) -> ()",
+    "rms_norm": "(Tensor(a!) result, Tensor input, Tensor? weight, float epsilon) -> ()",
+    "fused_add_rms_norm": "(Tensor(a!) input, Tensor(b!) residual, Tensor? weight, float epsilon) -> ()",
+    "rms_norm_dynamic_per_token_quant":
+        "(Tensor(a!) result, Tensor input, Tensor weight, Tensor(b!) scale, float epsilon, Tensor? scale_ub, "
+        "Tensor(c!)? residual) -> ()",
+    "rotary_embedding":
+        "(Tensor positions, Tensor(a!) query, Tensor(b!)? key, int head_size, Tensor cos_sin_cache, bool is_neox, "
+        "int rope_dim_offset=0, bool inverse=False) -> ()",
+    "silu_and_mul": "(Tensor(a!) result, Tensor input) -> ()",
+    "silu_and_mul_nvfp4_quant":
+        "(Tensor(a!) result, Tensor(b!) result_block_scale, Tensor input, Tensor input_global_scale) -> ()",
     "paged_attention_decode":
         "(Tensor(a!) out, Tensor query, Tensor key_cache, Tensor value_cache, Tensor block_table, Tensor seq_lens, "
         "float scale, int max_seq_len, str kv_cache_dtype, Tensor? k_scale, Tensor? v_scale, int num_splits, "
@@ -119,7 +135,46 @@ def _paged_attention_decode(out, query, key_cache, value_cache, block_table, seq
                                sliding_window, token_to_seq)
 
 
+def _need_weight(weight, what):
+    if weight is None:
+        raise RuntimeError(f"b200::{what}: weight=None (norm without scale) is not built")
+    return weight
+
+
+def _rms_norm(result, input, weight, epsilon):
+    ops.rms_norm(result, input, _need_weight(weight, "rms_norm"), epsilon)
+
+
+def _fused_add_rms_norm(input, residual, weight, epsilon):
+    ops.fused_add_rms_norm(input, residual, _need_weight(weight, "fused_add_rms_norm"), epsilon)
+
+
+def _rms_norm_dynamic_per_token_quant(result, input, weight, scale, epsilon, scale_ub, residual):
+    ops.rms_norm_dynamic_per_token_quant(input, weight, epsilon, scale_ub=scale_ub, residual=residual, output=result,
+                                         scales=scale)
+
+
+def _rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox, rope_dim_offset=0, inverse=False):
+    if rope_dim_offset != 0 or inverse or key is None:
+        raise RuntimeError("b200::rotary_embedding: rope_dim_offset / inverse / key=None are not built")
+    ops.rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox)
+
+
+def _silu_and_mul(result, input):
+    ops.silu_and_mul(result, input)
+
+
+def _silu_and_mul_nvfp4_quant(result, result_block_scale, input, input_global_scale):
+    ops.silu_and_mul_nvfp4_quant(result, result_block_scale, input, input_global_scale)
+
+
 _IMPLS = {
+    "rms_norm": _rms_norm,
+    "fused_add_rms_norm": _fused_add_rms_norm,
+    "rms_norm_dynamic_per_token_quant": _rms_norm_dynamic_per_token_quant,
+    "rotary_embedding": _rotary_embedding,
+    "silu_and_mul": _silu_and_mul,
+    "silu_and_mul_nvfp4_quant": _silu_and_mul_nvfp4_quant,
     "reshape_and_cache_flash": _reshape_and_cache_flash,
     "cutlass_scaled_mm": _cutlass_scaled_mm,
     "cutlass_scaled_fp4_mm": _cutlass_scaled_fp4_mm,

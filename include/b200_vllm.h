@@ -270,6 +270,10 @@ int b200_rms_norm_nvfp4_quant(void* result, void* result_block_scale, const void
  * A [M][K] e4m3 row-major (lda elements), B "column-major [K][N]" i.e. stored
  * [N][K] K-contiguous (ldb elements), out row-major (ldc), fp32 accumulate.
  * a_scales has 1 or M entries, b_scales 1 or N.  K % 16 == 0, N % 16 == 0.
+ * Differs from the reference in one precondition: for M <= 256 the WEIGHT operand `b` is prefetched before the
+ * kernel waits for its stream predecessors (programmatic dependent launch, see b200_set_pdl), so `b` must not be
+ * written by a kernel of this library that is still in flight on the same stream when the GEMM is launched
+ * (weights quantised at load time - the only case in vLLM - satisfy this; b200_set_pdl(0) removes the condition).
  * ---------------------------------------------------------------------- */
 int b200_scaled_mm_fp8(void* out, const void* a, const void* b,
                        const float* a_scales, const float* b_scales,

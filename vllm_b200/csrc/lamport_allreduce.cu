@@ -90,10 +90,11 @@ template <typename T> __device__ __forceinline__ uint4 lp_round(const float (&ac
   return o;
 }
 
-// The reduction proper.  On return `sum_of(row_slot k, vector v)` can be read through lp_result(): for the one-shot
-// form it sums on the fly, for the two-shot form it reads the gather area.  To keep one code path for the epilogues
-// the function hands every summed 16-byte vector of this CTA's rows to `sink(row, v, uint4 sum_in_T)`.
-// `row_done(row)` is called by ALL threads of the CTA after the row's last vector went through `sink`.
+// The reduction proper, for the rows this CTA owns.  One code path for all epilogues: every summed 16-byte vector
+// (8 values of T: fp32 accumulation in rank order, rounded once) is handed to `sink(row, v, sum)` by the thread
+// that owns vector v of the row (v = tid, tid + blockDim, ...), and `row_done(row)` is then called by ALL threads of
+// the CTA (it may contain __syncthreads).  The one-shot form sums while it polls; the two-shot form reads the
+// gather area.
 template <typename T, typename Sink, typename RowDone>
 __device__ __forceinline__ void lp_all_reduce_rows(const LpArgs& a, const T* __restrict__ in, int rank, Sink&& sink,
                                                    RowDone&& row_done) {

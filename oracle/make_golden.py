@@ -238,6 +238,21 @@ def main() -> None:
         fm.append(dict(a_packed=ap, b_packed=bp, sfa=asf.view(torch.uint8), sfb=bsf.view(torch.uint8),
                        alpha=(1.0 / (gsa * gsb)), out=out, a_dq=a_dq, b_dq=b_dq))
     torch.save(fm, OUT / "nvfp4_mm.pt")
+    # ---------------- fused SiLU*mul + NVFP4 quant: the reference test's own recipe
+    # (tests/kernels/quantization/test_silu_mul_nvfp4_quant.py:36-51: SiluAndMul.forward_native, then the NVFP4
+    #  quantiser with global scale 448*6/amax; its bar is atol = rtol = 3e-1 on the dequantised values)
+    import torch.nn.functional as F
+    g = gen(42)
+    sm = []
+    for (m, n2, dtype) in [(128, 256, torch.float16), (128, 128, torch.bfloat16), (256, 256, torch.bfloat16),
+                           (37, 96, torch.bfloat16)]:
+        x = torch.randn(m, n2, generator=g).to(dtype)
+        d = n2 // 2
+        ref_out = F.silu(x[..., :d]) * x[..., d:]                     # SiluAndMul.forward_native (activation.py:134-137)
+        gs = (448.0 * 6.0 / ref_out.abs().max().to(torch.float32)).reshape(1)
+        vals, sf = ns["ref_nvfp4_quant"](ref_out, gs)
+        sm.append(dict(x=x, global_scale=gs, ref_values=vals, ref_scale=sf))
+    torch.save(sm, OUT / "silu_mul_nvfp4_quant.pt")
     total = sum(p.stat().st_size for p in OUT.glob("*.pt"))
     print(f"wrote {len(list(OUT.glob('*.pt')))} fixtures, {total / 1e6:.1f} MB, to {OUT}")
 

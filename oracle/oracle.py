@@ -339,3 +339,27 @@ def rms_norm_dynamic_per_token_quant(x, w, eps, scale_ub=None, residual=None):
     y = ((xf * rms).to(x.dtype).float() * w.float()).to(x.dtype).float()
     q, s = dynamic_per_token_scaled_fp8_quant(y, scale_ub)
     return q, s, new_res
+
+
+# ------------------------------------------------------------- fused NVFP4 producers
+def silu_and_mul_nvfp4_quant(x, global_scale):
+    """csrc/libtorch_stable/quantization/fp4/activation_nvfp4_quant_fusion_kernels.cu:39-113 with
+    nvfp4_utils.cuh:304-329 (compute_silu_mul): silu(gate) * up is formed in fp32 and rounded to the activation
+    dtype ONCE (one rounding fewer than silu_and_mul followed by scaled_fp4_quant), then quantised like
+    scaled_fp4_quant with the swizzled scale layout.  Returns (packed codes, swizzled scale bytes)."""
+    d = x.shape[-1] // 2
+    g, u = x[..., :d].float(), x[..., d:].float()
+    act = ((g / (1.0 + torch.exp(-g))) * u).to(x.dtype)
+    return scaled_fp4_quant(act, global_scale, swizzled=True)
+
+
+def rms_norm_nvfp4_quant(x, w, eps, global_scale, residual=None):
+    """No reference kernel: the reference's NVFP4 path runs fused_add_rms_norm (layernorm_kernels.cu) and then
+    scaled_fp4_quant (nvfp4_quant_kernels.cu); this is that composition.  Returns (packed, swizzled scales,
+    new_residual | None)."""
+    if residual is not None:
+        y, new_res = rms_norm(x, w, eps, residual=residual)
+    else:
+        y, new_res = rms_norm(x, w, eps), None
+    packed, sf = scaled_fp4_quant(y, global_scale, swizzled=True)
+    return packed, sf, new_res
